@@ -1,0 +1,20 @@
+// crt_bvh.h -- host-side BVH construction for the scene-upload module.
+#pragma once
+#include <stdint.h>
+#include <vector>
+
+namespace crt {
+
+struct BvhResult {
+  std::vector<float> nodes;        // 16 floats (4 x float4) per BVH2 node, device layout (crt_device.cuh traverse())
+  std::vector<uint32_t> tri_src;   // triangle slot (leaf order) -> position in the primitives binding
+  uint32_t n_nodes = 0;
+  uint32_t max_depth = 0;
+  float pad = 0.0f;
+};
+
+// prims: binding-8 bytes (80-byte records); tri_pos: positions of the category-2 records.
+// Deterministic: the result does not depend on the number of threads.
+void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n_threads, BvhResult& out);
+
+}  // namespace crt

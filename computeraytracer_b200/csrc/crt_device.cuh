@@ -1,0 +1,427 @@
+// crt_device.cuh -- device-side building blocks of the path tracer (sm_100a).
+//
+// Everything here follows the live code of the reference's src/shaders/ComputeShader.wgsl
+// ("CS:" citations) under the numerics contract of DESIGN.md: f32 throughout, no implicit
+// contraction (-fmad=false), explicit fmaf in dot/cross/ray_at, IEEE div/sqrt, transcendental
+// functions from include/crt_detmath.h.  Ray-invariant quantities (unit normals, e.e, r^2,
+// camera frame) are hoisted to scene upload; the hoists are bit-identical to evaluating them
+// per ray, which the parity tests against the CPU oracle (which does not hoist) prove.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/crt.h"
+#include "../../include/crt_detmath.h"
+
+#define CRT_PI_F 3.14159265359f         // CS:11
+#define CRT_INFINITY_F 2139095040.0f    // CS:12: f32(0x7F800000 as an integer), not +inf
+#define CRT_MAX_U32 0xFFFFFFFFu         // CS:13
+#define CRT_LAMBDA_RANGE 301u           // CS:16-17, 318
+#define CRT_MAT_DIFFUSE 0u              // CS:18
+#define CRT_MAT_LIGHT 1u                // CS:19
+#define CRT_MAT_GLASS 2u                // CS:20
+
+#define CRT_LIN_PARAM_MAX 64            // patches/spheres carried in kernel-parameter (constant-bank) space
+#define CRT_LIGHT_PARAM_MAX 8
+#define CRT_TRI_REF 0x80000000u         // Hit::ref flag: slot in the triangle array
+#define CRT_BVH_STACK 64
+
+// meta word: category | material << 2 | emission << 4 | reflectance << 16
+#define CRT_META_CAT(m) ((m)&3u)
+#define CRT_META_MAT(m) (((m) >> 2) & 3u)
+#define CRT_META_EMIS(m) (((m) >> 4) & 0xFFFu)
+#define CRT_META_REFL(m) (((m) >> 16) & 0xFFFu)
+
+struct LinPrim {   // one patch or sphere of the linear list, 64 bytes
+  float4 A;        // patch: unit normal of cross(e1,e2) | sphere: centre       ; w = bits(primitive index)
+  float4 B;        // patch: origin                      | sphere: (r*r, r, 0)  ; w = bits(meta)
+  float4 C;        // patch: edge1, w = dot(e1,e1)
+  float4 D;        // patch: edge2, w = dot(e2,e2)
+};
+
+struct LightRec {  // one entry of binding 7 with compute_light_pdf's invariants hoisted (CS:363-364)
+  float4 d1;       // origin;  w = bits(data4.w) (primitive index of the light)
+  float4 d2;       // edge1;   w = bits(data4.x) (emission spectrum)
+  float4 d3;       // edge2;   w = light_area_pdf = 1 / (|d2| * |d3|)
+};
+
+struct DevScene {
+  // camera (pixel-invariant part of camera_ray, CS:478-487)
+  float eye[3], hor[3], ver[3], llc[3];
+  uint32_t W, H;
+  // params (crt_params)
+  uint32_t max_depth, grid_size;
+  float t_min, exposure;
+  // tables
+  const float* spectra;    // n_spectra x 301
+  const float* cie;        // 3 x 471
+  uint32_t n_spectra;
+  // lights
+  uint32_t n_lights;
+  const LightRec* lights_g;       // all lights (global memory)
+  // linear list
+  uint32_t n_lin;
+  const LinPrim* lin_g;           // all entries (global); the first CRT_LIN_PARAM_MAX are mirrored below
+  // triangles + BVH
+  uint32_t n_tri, n_nodes;
+  const float4* tri;              // 3 x float4 per triangle, BVH leaf order
+  const float4* nodes;            // 4 x float4 per BVH2 node
+  uint32_t shadow_closest;        // 1: some light's primitive is a triangle -> shadow rays need closest-hit
+  // sharding
+  uint32_t rank, world, shard_mode;
+  uint32_t tiles_x, tiles_y;
+  LightRec lights_c[CRT_LIGHT_PARAM_MAX];
+  LinPrim lin_c[CRT_LIN_PARAM_MAX];
+};
+
+struct Stats {
+  uint32_t prim_tests, node_visits, tri_tests, rand_calls;
+};
+
+// ------------------------------------------------------------------------------------------------ vectors
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 v3(const float4& a) { return v3(a.x, a.y, a.z); }
+__device__ __forceinline__ V3 v3(const float* p) { return v3(p[0], p[1], p[2]); }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return v3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+  return v3(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));
+}
+__device__ __forceinline__ float length(V3 a) { return sqrtf(dot(a, a)); }
+__device__ __forceinline__ V3 normalize(V3 a) { return a / length(a); }
+__device__ __forceinline__ V3 madd(V3 a, float s, V3 b) { return v3(fmaf(s, b.x, a.x), fmaf(s, b.y, a.y), fmaf(s, b.z, a.z)); }
+__device__ __forceinline__ uint32_t f2u_sat(float f) { return __float2uint_rz(f); }  // WGSL u32(f32): saturating, NaN -> 0
+
+// ------------------------------------------------------------------------------------------------ RNG, CS:865-899
+__device__ __forceinline__ uint32_t tea(uint32_t v0, uint32_t v1) {
+  uint32_t s0 = 0;
+#pragma unroll
+  for (int n = 0; n < 16; n++) {
+    s0 += 0x9e3779b9u;
+    v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + s0) ^ ((v1 >> 5) + 0xc8013ea4u);
+    v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + s0) ^ ((v0 >> 5) + 0x7e95761eu);
+  }
+  return v0;
+}
+
+struct Rng { uint32_t x, y, z, w; };
+
+__device__ __forceinline__ float rnd(Rng& s) {
+  s.x = s.x * 1664525u + 1013904223u; s.y = s.y * 1664525u + 1013904223u;
+  s.z = s.z * 1664525u + 1013904223u; s.w = s.w * 1664525u + 1013904223u;
+  s.x += s.y * s.w; s.y += s.z * s.x; s.z += s.x * s.y; s.w += s.y * s.z;
+  s.x ^= s.x >> 16; s.y ^= s.y >> 16; s.z ^= s.z >> 16; s.w ^= s.w >> 16;
+  s.x += s.y * s.w; s.y += s.z * s.x; s.z += s.x * s.y; s.w += s.y * s.z;
+  return (float)(s.x & 0x00ffffffu) / 16777216.0f;
+}
+
+// ------------------------------------------------------------------------------------------------ intersection
+struct Hit {
+  float t;        // context.t_max after the scan (CS:577); CRT_INFINITY_F when nothing was accepted
+  uint32_t idx;   // context.index: primitive index of the winner, CRT_MAX_U32 on a miss
+  uint32_t ref;   // where the winner lives: linear-list slot, or CRT_TRI_REF | triangle slot
+};
+
+// ray_intersection for one linear-list entry, CS:520-632, sequential semantics (called in index order).
+__device__ __forceinline__ void test_lin(const LinPrim& p, uint32_t slot, V3 o, V3 d, uint32_t exclude, float t_min, Hit& h) {
+  uint32_t index = __float_as_uint(p.A.w);
+  if (exclude == index) return;                      // CS:529 / CS:588
+  uint32_t meta = __float_as_uint(p.B.w);
+  if (CRT_META_CAT(meta) == 0u) {
+    V3 n = v3(p.A);
+    float ndotd = dot(n, d);
+    // CS:541-546: flipping the normal negates n.d exactly, so |n.d| and the quotient below are unchanged
+    if (fabsf(ndotd) < 0.0001f) return;
+    V3 p0 = v3(p.B);
+    float t = dot(n, p0 - o) / ndotd;                // CS:554
+    if (t < t_min || t > h.t) return;                // CS:557
+    V3 m = madd(o, t, d) - p0;                       // CS:561-562
+    float u = dot(m, v3(p.C)) / p.C.w;               // CS:563
+    float v = dot(m, v3(p.D)) / p.D.w;               // CS:564
+    if (u < 0.0f || u > 1.0f || v < 0.0f || v > 1.0f) return;  // CS:566
+    h.t = t; h.idx = index; h.ref = slot;
+  } else {
+    V3 co = o - v3(p.A);                             // CS:597
+    float a = dot(d, d);
+    float b = 2.0f * dot(d, co);
+    float c = dot(co, co) - p.B.x;
+    float disc = fmaf(b, b, -((4.0f * a) * c));      // CS:601
+    if (disc <= 0.0f) return;
+    float sq = sqrtf(disc);
+    float t = (-b - sq) / (2.0f * a);                // CS:606
+    if (t < t_min || t > h.t) {
+      t = (-b + sq) / (2.0f * a);                    // CS:611
+      if (t < t_min || t > h.t) return;
+    }
+    h.t = t; h.idx = index; h.ref = slot;
+  }
+}
+
+// Triangle extension (category 2): Moller-Trumbore on (v0, e1, e2), accept-if-good so NaN never hits.
+// Returns true and t when the ray hits inside [t_min, t_max].
+__device__ __forceinline__ bool test_tri(float4 T0, float4 T1, float4 T2, V3 o, V3 d, float t_min, float t_max, float& t_out) {
+  V3 e1 = v3(T1), e2 = v3(T2);
+  V3 pvec = cross(d, e2);
+  float det = dot(e1, pvec);
+  if (!(fabsf(det) >= 1e-8f)) return false;
+  float inv = 1.0f / det;
+  V3 tvec = o - v3(T0);
+  float u = dot(tvec, pvec) * inv;
+  if (!(u >= 0.0f && u <= 1.0f)) return false;
+  V3 qvec = cross(tvec, e1);
+  float v = dot(d, qvec) * inv;
+  if (!(v >= 0.0f && u + v <= 1.0f)) return false;
+  float t = dot(e2, qvec) * inv;
+  if (!(t >= t_min && t <= t_max)) return false;
+  t_out = t;
+  return true;
+}
+
+// BVH2 over the triangles.  Node = 4 x float4:
+//   n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)   n1 = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
+//   n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)   n3 = bits(child0, child1, -, -)
+// child >= 0: inner node index; child < 0: leaf, ~child = first_triangle << 3 | (count - 1).
+// Boxes are padded at build time so that culling with (tnear <= best.t) never drops a primitive the
+// linear scan would accept (DESIGN.md "Conservative culling"); equal-t ties go to the higher
+// primitive index, which is what the reference's in-order scan with `t > t_max` rejection yields.
+template <bool ANYHIT, bool STATS>
+__device__ __forceinline__ void traverse(const DevScene& sc, V3 o, V3 d, uint32_t exclude, float t_min, Hit& h, Stats& st) {
+  if (sc.n_tri == 0) return;
+  const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
+  int stack[CRT_BVH_STACK];
+  int sp = 0;
+  int node = 0;   // root is always an inner node (a lone leaf is wrapped at build time)
+  const float4* __restrict__ nodes = sc.nodes;
+  const float4* __restrict__ tris = sc.tri;
+  for (;;) {
+    if (node >= 0) {
+      const float4 n0 = __ldg(&nodes[4 * node + 0]);
+      const float4 n1 = __ldg(&nodes[4 * node + 1]);
+      const float4 n2 = __ldg(&nodes[4 * node + 2]);
+      const float4 n3 = __ldg(&nodes[4 * node + 3]);
+      if (STATS) st.node_visits++;
+      float a0 = (n0.x - o.x) * idx, a1 = (n0.y - o.x) * idx;
+      float b0 = (n0.z - o.y) * idy, b1 = (n0.w - o.y) * idy;
+      float c0 = (n2.x - o.z) * idz, c1 = (n2.y - o.z) * idz;
+      float tn0 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), t_min));
+      float tf0 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), h.t));
+      a0 = (n1.x - o.x) * idx; a1 = (n1.y - o.x) * idx;
+      b0 = (n1.z - o.y) * idy; b1 = (n1.w - o.y) * idy;
+      c0 = (n2.z - o.z) * idz; c1 = (n2.w - o.z) * idz;
+      float tn1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), t_min));
+      float tf1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), h.t));
+      const bool hit0 = tn0 <= tf0, hit1 = tn1 <= tf1;
+      const int ch0 = __float_as_int(n3.x), ch1 = __float_as_int(n3.y);
+      if (hit0 && hit1) {
+        const bool swap = tn1 < tn0;
+        node = swap ? ch1 : ch0;
+        stack[sp++] = swap ? ch0 : ch1;
+      } else if (hit0) {
+        node = ch0;
+      } else if (hit1) {
+        node = ch1;
+      } else {
+        if (sp == 0) return;
+        node = stack[--sp];
+      }
+    } else {
+      const uint32_t leaf = (uint32_t)(~node);
+      const uint32_t first = leaf >> 3, count = (leaf & 7u) + 1u;
+      for (uint32_t i = 0; i < count; i++) {
+        const uint32_t slot = first + i;
+        const float4 T0 = __ldg(&tris[3 * slot + 0]);
+        const float4 T1 = __ldg(&tris[3 * slot + 1]);
+        const float4 T2 = __ldg(&tris[3 * slot + 2]);
+        if (STATS) st.tri_tests++;
+        const uint32_t index = __float_as_uint(T0.w);
+        if (index == exclude) continue;
+        float t;
+        if (test_tri(T0, T1, T2, o, d, t_min, h.t, t)) {
+          if (t < h.t || h.idx == CRT_MAX_U32 || index > h.idx) {
+            h.t = t; h.idx = index; h.ref = CRT_TRI_REF | slot;
+            if (ANYHIT) return;
+          }
+        }
+      }
+      if (sp == 0) return;
+      node = stack[--sp];
+    }
+  }
+}
+
+// intersect(), CS:503-518: closest accepted t over all primitives, ties to the highest index.
+template <bool STATS>
+__device__ __forceinline__ Hit intersect(const DevScene& sc, V3 o, V3 d, uint32_t exclude, Stats& st) {
+  Hit h; h.t = CRT_INFINITY_F; h.idx = CRT_MAX_U32; h.ref = 0;
+  const uint32_t n_c = sc.n_lin < CRT_LIN_PARAM_MAX ? sc.n_lin : CRT_LIN_PARAM_MAX;
+  for (uint32_t i = 0; i < n_c; i++) test_lin(sc.lin_c[i], i, o, d, exclude, sc.t_min, h);
+  for (uint32_t i = CRT_LIN_PARAM_MAX; i < sc.n_lin; i++) test_lin(sc.lin_g[i], i, o, d, exclude, sc.t_min, h);
+  if (STATS) st.prim_tests += sc.n_lin;
+  traverse<false, STATS>(sc, o, d, exclude, sc.t_min, h, st);
+  return h;
+}
+
+// shadow_intersect(), CS:697-705: the reference runs the full closest-hit scan and then keeps the hit
+// only if the winner is `include`.  The outcome (winner == include or not) is all the caller uses, so
+// once the linear list has produced the light at distance t, any triangle accepted at <= t (under the
+// tie rule) settles it: an any-hit traversal bounded by t gives the identical boolean.
+template <bool STATS>
+__device__ __forceinline__ Hit shadow_intersect(const DevScene& sc, V3 o, V3 d, uint32_t include, uint32_t exclude, Stats& st) {
+  Hit h; h.t = CRT_INFINITY_F; h.idx = CRT_MAX_U32; h.ref = 0;
+  const uint32_t n_c = sc.n_lin < CRT_LIN_PARAM_MAX ? sc.n_lin : CRT_LIN_PARAM_MAX;
+  for (uint32_t i = 0; i < n_c; i++) test_lin(sc.lin_c[i], i, o, d, exclude, sc.t_min, h);
+  for (uint32_t i = CRT_LIN_PARAM_MAX; i < sc.n_lin; i++) test_lin(sc.lin_g[i], i, o, d, exclude, sc.t_min, h);
+  if (STATS) st.prim_tests += sc.n_lin;
+  if (sc.shadow_closest) {
+    traverse<false, STATS>(sc, o, d, exclude, sc.t_min, h, st);
+  } else if (h.idx == include) {
+    traverse<true, STATS>(sc, o, d, exclude, sc.t_min, h, st);
+  }
+  return h;
+}
+
+// The fields of ShapeIntersection (CS:54-60) for the winner, rebuilt after the scan.
+struct Surface {
+  V3 position, normal;
+  uint32_t meta;
+};
+
+__device__ __forceinline__ Surface surface_of(const DevScene& sc, const Hit& h, V3 o, V3 d) {
+  Surface s;
+  s.position = madd(o, h.t, d);                       // ray_at, CS:304-307
+  if (h.ref & CRT_TRI_REF) {
+    const uint32_t slot = h.ref & ~CRT_TRI_REF;
+    const float4 T1 = __ldg(&sc.tri[3 * slot + 1]);
+    const float4 T2 = __ldg(&sc.tri[3 * slot + 2]);
+    V3 n = normalize(cross(v3(T1), v3(T2)));
+    if (dot(n, d) > 0.0f) n = -n;
+    s.normal = n;
+    s.meta = __float_as_uint(T1.w);
+  } else {
+    const LinPrim& p = (h.ref < CRT_LIN_PARAM_MAX) ? sc.lin_c[h.ref] : sc.lin_g[h.ref];
+    s.meta = __float_as_uint(p.B.w);
+    if (CRT_META_CAT(s.meta) == 0u) {
+      V3 n = v3(p.A);
+      if (dot(n, d) > 0.0f) n = -n;                   // CS:541-544
+      s.normal = n;
+    } else {
+      s.normal = normalize(s.position - v3(p.A));     // CS:618 (outward, never flipped)
+    }
+  }
+  return s;
+}
+
+// ------------------------------------------------------------------------------------------------ shading helpers
+__device__ __forceinline__ void wavelengths(uint32_t l0, uint32_t lam[4]) {   // CS:321
+  lam[0] = l0; lam[1] = (l0 + 4u) % CRT_LAMBDA_RANGE; lam[2] = (l0 + 8u) % CRT_LAMBDA_RANGE; lam[3] = (l0 + 12u) % CRT_LAMBDA_RANGE;
+}
+
+__device__ __forceinline__ float4 sample_spectrum(const float* __restrict__ spectra, uint32_t n_spectra, uint32_t index, const uint32_t lam[4]) {
+  if (index >= n_spectra) index = n_spectra - 1;      // out-of-bounds pin: clamp
+  const float* s = spectra + index * CRT_LAMBDA_RANGE;
+  return make_float4(s[lam[0]], s[lam[1]], s[lam[2]], s[lam[3]]);
+}
+
+__device__ __forceinline__ float power_heuristic(float f_pdf, float g_pdf) {  // CS:297-302, nf = ng = 1
+  float f = 1.0f * f_pdf, g = 1.0f * g_pdf;
+  return (f * f) / (f * f + g * g);
+}
+
+__device__ __forceinline__ const LightRec& light_at(const DevScene& sc, uint32_t li) {
+  if (li >= sc.n_lights) li = sc.n_lights - 1;         // CS:362 reads out of bounds in the default scene: clamp pin
+  return (li < CRT_LIGHT_PARAM_MAX) ? sc.lights_c[li] : sc.lights_g[li];
+}
+
+// compute_light_pdf, CS:357-377
+__device__ __forceinline__ float compute_light_pdf(const DevScene& sc, uint32_t emission_index, V3 normal, V3 position, V3 ray_origin, V3 ray_direction) {
+  const LightRec& light = light_at(sc, emission_index);
+  float light_area_pdf = light.d3.w;
+  float abs_cos_theta = fmaxf(0.00001f, fabsf(dot(normal, -ray_direction)));
+  float distance = length(position - ray_origin);
+  float distance_squared = distance * distance;
+  float geometric_term = abs_cos_theta / distance_squared;
+  float light_solid_angle_pdf = light_area_pdf / geometric_term;
+  float light_selection_pdf = 1.0f / (float)sc.n_lights;
+  return light_selection_pdf * light_solid_angle_pdf;
+}
+
+// cosine_weighted_sample_hemisphere, CS:751-774 (u, v drawn by the caller in that order)
+__device__ __forceinline__ V3 cosine_hemisphere(V3 normal, float u, float v, float& pdf) {
+  float r = sqrtf(u);
+  float theta = (2.0f * CRT_PI_F) * v;
+  float sn, cs;
+  crt_sincosf(theta, &sn, &cs);
+  float x = r * cs, y = r * sn;
+  float z = sqrtf(fmaxf(0.0f, 1.0f - u));
+  V3 up = (fabsf(normal.z) < 0.999f) ? v3(0.0f, 0.0f, 1.0f) : v3(1.0f, 0.0f, 0.0f);
+  V3 tangent = normalize(cross(up, normal));
+  V3 bitangent = cross(normal, tangent);
+  pdf = z / CRT_PI_F;
+  return v3(fmaf(normal.x, z, fmaf(bitangent.x, y, tangent.x * x)),
+            fmaf(normal.y, z, fmaf(bitangent.y, y, tangent.y * x)),
+            fmaf(normal.z, z, fmaf(bitangent.z, y, tangent.z * x)));
+}
+
+// fresnel_s, CS:814-837
+__device__ __forceinline__ float fresnel_s(V3 ray_dir, V3 normal, float eta1, float eta2) {
+  float cosi = fminf(fmaxf(dot(ray_dir, normal), -1.0f), 1.0f);
+  float eta = eta1 / eta2;
+  if (cosi > 0.0f) eta = eta2 / eta1;
+  float sint2 = (eta * eta) * (1.0f - cosi * cosi);
+  if (sint2 > 1.0f) return 1.0f;
+  float cost = sqrtf(1.0f - sint2);
+  cosi = fabsf(cosi);
+  float Rs = ((eta1 * cosi) - (eta2 * cost)) / ((eta1 * cosi) + (eta2 * cost));
+  float Rp = ((eta2 * cosi) - (eta1 * cost)) / ((eta2 * cosi) + (eta1 * cost));
+  return (Rs * Rs + Rp * Rp) / 2.0f;
+}
+
+__device__ __forceinline__ V3 reflect(V3 e1, V3 e2) {   // WGSL reflect
+  float k = 2.0f * dot(e2, e1);
+  return madd(e1, -k, e2);
+}
+__device__ __forceinline__ V3 refract(V3 e1, V3 e2, float e3) {   // WGSL refract
+  float dd = dot(e2, e1);
+  float k = 1.0f - (e3 * e3) * (1.0f - dd * dd);
+  if (k < 0.0f) return v3(0.0f, 0.0f, 0.0f);
+  float s = fmaf(e3, dd, sqrtf(k));
+  return madd(e1 * e3, -s, e2);
+}
+
+// spectral_to_xyz, CS:411-426
+__device__ __forceinline__ V3 spectral_to_xyz(const float* __restrict__ cie, float4 L, const uint32_t lam[4]) {
+  float o[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const float* c = cie + 471 * k + 40;
+    float s = fmaf(c[lam[3]], L.w, fmaf(c[lam[2]], L.z, fmaf(c[lam[1]], L.y, c[lam[0]] * L.x)));
+    o[k] = (s * 300.0f) / 427.42758f;
+  }
+  return v3(o[0], o[1], o[2]);
+}
+
+// epilogue of main, CS:109-115: average, XYZ -> linear sRGB, tone map, gamma (with the reference's green
+// quirk, CS:453), rgba8unorm store
+__device__ __forceinline__ uint32_t unorm8(float c) {
+  if (c != c) return 0u;
+  c = fminf(fmaxf(c, 0.0f), 1.0f);
+  return (uint32_t)floorf(c * 255.0f + 0.5f);
+}
+__device__ __forceinline__ uint32_t resolve_pixel(float X, float Y, float Z, uint32_t sample, float exposure) {
+  float fs = (float)sample;
+  X = X / fs; Y = Y / fs; Z = Z / fs;
+  float r = fmaf(-0.4985314f, Z, fmaf(-1.5371385f, Y, 3.2404542f * X));
+  float g = fmaf(0.0415560f, Z, fmaf(1.8760108f, Y, -0.9692660f * X));
+  float b = fmaf(1.0572252f, Z, fmaf(-0.2040259f, Y, 0.0556434f * X));
+  r = 1.0f - crt_expf(-r * exposure); g = 1.0f - crt_expf(-g * exposure); b = 1.0f - crt_expf(-b * exposure);
+  r = r < 0.0031308f ? r * 12.92f : 1.055f * crt_powf(r, 0.41666666f) - 0.055f;
+  g = g < 0.0031308f ? g * (12.92f * g) : 1.055f * crt_powf(g, 0.41666666f) - 0.055f;
+  b = b < 0.0031308f ? 12.92f * b : 1.055f * crt_powf(b, 0.41666666f) - 0.055f;
+  return unorm8(r) | (unorm8(g) << 8) | (unorm8(b) << 16) | 0xFF000000u;
+}

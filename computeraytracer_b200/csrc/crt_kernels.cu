@@ -1,0 +1,475 @@
+// crt_kernels.cu -- CUDA kernels of libcrt (sm_100a).
+//
+//   pt_megakernel      the hot path: ComputeShader.wgsl main() (CS:77-117) for n frames, as a
+//                      persistent-thread kernel with per-lane path regeneration
+//   trace_rays_kernel  test hook: intersect() (CS:503-518) on caller-supplied rays
+//   resolve_kernel     epilogue of main (CS:109-115) over the whole accumulator
+//   repack_* kernels   the scene-upload module: reference-layout buffers -> SoA device layouts
+//
+// Build flags matter for parity: -fmad=false -prec-div=true -prec-sqrt=true -ftz=false.
+#include "crt_device.cuh"
+#include "crt_kernels.h"
+
+#define CRT_BLOCK 128
+
+// ------------------------------------------------------------------------------------------------ upload module
+// 80-byte Primitive record (CS:41-47; written by main.js:211-246)
+struct RawPrim {
+  uint32_t category, pad0[3];
+  float d1[3]; uint32_t pad1;
+  float d2[3]; uint32_t pad2;
+  float d3[3]; uint32_t pad3;
+  uint32_t d4[4];
+};
+
+__device__ __forceinline__ uint32_t make_meta(const RawPrim& p) {
+  uint32_t mat = p.d4[2] > 3u ? 3u : p.d4[2];          // anything that is not diffuse/light/glass takes no branch
+  uint32_t emis = p.d4[0] > 0xFFFu ? 0xFFFu : p.d4[0];
+  uint32_t refl = p.d4[1] > 0xFFFu ? 0xFFFu : p.d4[1];
+  return (p.category & 3u) | (mat << 2) | (emis << 4) | (refl << 16);
+}
+
+// linear list: the patches and spheres of binding 8, in index order; lin_src[i] = position in prims[]
+__global__ void repack_lin_kernel(const RawPrim* __restrict__ prims, const uint32_t* __restrict__ lin_src, uint32_t n, LinPrim* __restrict__ out) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const RawPrim p = prims[lin_src[i]];
+  LinPrim q;
+  const float idxf = __uint_as_float(p.d4[3]);
+  const float metaf = __uint_as_float(make_meta(p));
+  if (p.category == 0u) {
+    V3 e1 = v3(p.d2), e2 = v3(p.d3);
+    V3 n_ = normalize(cross(e1, e2));                  // CS:536
+    q.A = make_float4(n_.x, n_.y, n_.z, idxf);
+    q.B = make_float4(p.d1[0], p.d1[1], p.d1[2], metaf);
+    q.C = make_float4(e1.x, e1.y, e1.z, dot(e1, e1));  // CS:563
+    q.D = make_float4(e2.x, e2.y, e2.z, dot(e2, e2));  // CS:564
+  } else {
+    float r = p.d2[0];                                 // CS:593-594
+    q.A = make_float4(p.d1[0], p.d1[1], p.d1[2], idxf);
+    q.B = make_float4(r * r, r, 0.0f, metaf);
+    q.C = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    q.D = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  }
+  out[i] = q;
+}
+
+// triangles in BVH leaf order: tri_src[slot] = position in prims[]
+__global__ void repack_tri_kernel(const RawPrim* __restrict__ prims, const uint32_t* __restrict__ tri_src, uint32_t n, float4* __restrict__ out) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const RawPrim p = prims[tri_src[i]];
+  out[3 * i + 0] = make_float4(p.d1[0], p.d1[1], p.d1[2], __uint_as_float(p.d4[3]));
+  out[3 * i + 1] = make_float4(p.d2[0], p.d2[1], p.d2[2], __uint_as_float(make_meta(p)));
+  out[3 * i + 2] = make_float4(p.d3[0], p.d3[1], p.d3[2], 0.0f);
+}
+
+__global__ void repack_lights_kernel(const RawPrim* __restrict__ lights, uint32_t n, LightRec* __restrict__ out) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const RawPrim p = lights[i];
+  float light_area = length(v3(p.d2)) * length(v3(p.d3));   // CS:363
+  LightRec q;
+  q.d1 = make_float4(p.d1[0], p.d1[1], p.d1[2], __uint_as_float(p.d4[3]));
+  q.d2 = make_float4(p.d2[0], p.d2[1], p.d2[2], __uint_as_float(p.d4[0]));
+  q.d3 = make_float4(p.d3[0], p.d3[1], p.d3[2], 1.0f / light_area);  // CS:364
+  out[i] = q;
+}
+
+// camera_basis + the pixel-invariant part of camera_ray, CS:470-487.  vph = 2*tan(fov/2) comes from the
+// host (double libm tan rounded once to f32: the tan pin of the numerics contract).
+__global__ void camera_setup_kernel(const float* __restrict__ cam, float vph, float* __restrict__ out12) {
+  V3 eye = v3(cam[0], cam[1], cam[2]), lookat = v3(cam[4], cam[5], cam[6]), up = v3(cam[8], cam[9], cam[10]);
+  V3 w = normalize(eye - lookat);
+  V3 u = normalize(cross(up, w));
+  V3 v = cross(w, u);
+  float aspect = cam[11] / cam[12];
+  float vpw = aspect * vph;
+  V3 hor = u * vpw, ver = v * vph;
+  V3 llc = ((eye - hor / 2.0f) - ver / 2.0f) - w;
+  out12[0] = eye.x; out12[1] = eye.y; out12[2] = eye.z;
+  out12[3] = hor.x; out12[4] = hor.y; out12[5] = hor.z;
+  out12[6] = ver.x; out12[7] = ver.y; out12[8] = ver.z;
+  out12[9] = llc.x; out12[10] = llc.y; out12[11] = llc.z;
+}
+
+// ------------------------------------------------------------------------------------------------ the hot path
+struct PathState {
+  V3 o, d;            // current ray: extension ray, or the shadow ray while phase == 1
+  float4 L, beta;     // accumulated_radiance, beta (CS:123-124)
+  float pdf;          // last_bounce_pdf (CS:125)
+  float etaScale;     // CS:130
+  uint32_t exclude;   // CS:126
+  uint32_t depth;     // CS:122
+  uint32_t lam0;      // first wavelength index; the other three follow (CS:321)
+  bool specular, in_transmission, shadow_phase;
+  // saved across the shadow ray of next-event estimation
+  V3 n;               // surface normal at the diffuse hit
+  uint32_t refl;      // reflectance spectrum of the diffuse hit
+  uint32_t light;     // sampled light
+};
+
+enum { TERM_MISS = CRT_CNT_TERM_MISS, TERM_RR = CRT_CNT_TERM_RR, TERM_LIGHT = CRT_CNT_TERM_LIGHT, TERM_DEPTH = CRT_CNT_TERM_DEPTH };
+
+// One intersect() call and everything that follows it up to the next one.  Returns false when the
+// path has terminated (its radiance is complete in ps.L).
+template <bool STATS>
+__device__ __forceinline__ bool path_step(const DevScene& sc, const float* __restrict__ spectra, PathState& ps, Rng& rng,
+                                          uint32_t& n_ext, uint32_t& n_shadow, Stats& st, uint32_t* term) {
+  uint32_t lam[4];
+  wavelengths(ps.lam0, lam);
+  if (!ps.shadow_phase) {
+    n_ext++;
+    const Hit h = intersect<STATS>(sc, ps.o, ps.d, ps.exclude, st);           // CS:135
+    if (h.idx == CRT_MAX_U32) { if (STATS) term[0] = TERM_MISS; return false; }  // CS:141-144
+    ps.exclude = h.idx;                                                       // CS:146
+    const Surface s = surface_of(sc, h, ps.o, ps.d);
+    const uint32_t material = CRT_META_MAT(s.meta);
+    if (material == CRT_MAT_LIGHT) {                                          // CS:149-164
+      const float4 le = sample_spectrum(spectra, sc.n_spectra, CRT_META_EMIS(s.meta), lam);
+      if (ps.depth == 0 || ps.specular) {
+        ps.L.x += ps.beta.x * le.x; ps.L.y += ps.beta.y * le.y; ps.L.z += ps.beta.z * le.z; ps.L.w += ps.beta.w * le.w;
+      } else {
+        const float pdf_l = compute_light_pdf(sc, CRT_META_EMIS(s.meta), s.normal, s.position, ps.o, ps.d);
+        const float w = power_heuristic(ps.pdf, pdf_l);
+        ps.L.x += (w * le.x) * ps.beta.x; ps.L.y += (w * le.y) * ps.beta.y;
+        ps.L.z += (w * le.z) * ps.beta.z; ps.L.w += (w * le.w) * ps.beta.w;
+      }
+      if (STATS) term[0] = TERM_LIGHT;
+      return false;
+    }
+    if (ps.depth >= sc.max_depth) { if (STATS) term[0] = TERM_DEPTH; return false; }  // CS:167-170
+    if (ps.in_transmission) {                                                 // CS:173-179
+      const float distance = length(ps.o - s.position);
+      const float4 ext = sample_spectrum(spectra, sc.n_spectra, sc.n_spectra - 1, lam);
+      ps.beta.x *= crt_expf(-ext.x * distance); ps.beta.y *= crt_expf(-ext.y * distance);
+      ps.beta.z *= crt_expf(-ext.z * distance); ps.beta.w *= crt_expf(-ext.w * distance);
+    }
+    if (material == CRT_MAT_DIFFUSE) {                                        // CS:182-204, first half
+      // sample_lights + sample_light, CS:341-355
+      const float u0 = rnd(rng);
+      uint32_t li = f2u_sat((float)sc.n_lights * u0);
+      if (li >= sc.n_lights) li = sc.n_lights - 1;
+      const LightRec& light = light_at(sc, li);
+      const float u = rnd(rng), v = rnd(rng);
+      if (STATS) st.rand_calls += 3;
+      const V3 point = madd(madd(v3(light.d1), u, v3(light.d2)), v, v3(light.d3));
+      const V3 light_dir = normalize(point - s.position);                     // CS:385
+      ps.n = s.normal; ps.refl = CRT_META_REFL(s.meta); ps.light = li;
+      ps.o = s.position; ps.d = light_dir;
+      ps.shadow_phase = true;
+      return true;                                                            // next step: the shadow ray
+    }
+    if (material == CRT_MAT_GLASS) {                                          // CS:208-276
+      const float eta1 = 1.0f, eta2 = 1.5f;
+      float eta = eta1 / eta2;
+      const float cos_theta = dot(s.normal, ps.d);
+      const float reflected = fresnel_s(ps.d, s.normal, eta1, eta2);
+      const float pr = reflected, pt = 1.0f - reflected;
+      const float u = rnd(rng);
+      if (STATS) st.rand_calls += 1;
+      V3 current_normal = s.normal;
+      if (cos_theta > 0.0f) { eta = 1.0f / eta; current_normal = -current_normal; }
+      V3 nd;
+      if (u < pr / (pr + pt)) {
+        nd = reflect(ps.d, current_normal);
+      } else {
+        nd = normalize(refract(ps.d, current_normal, eta));
+        const float e2 = eta * eta;
+        ps.beta.x *= e2; ps.beta.y *= e2; ps.beta.z *= e2; ps.beta.w *= e2;
+        ps.etaScale /= e2;
+        ps.in_transmission = !ps.in_transmission;
+      }
+      ps.o = s.position; ps.d = nd;
+      ps.specular = true; ps.exclude = CRT_MAX_U32;
+    }
+  } else {
+    // second half of the diffuse branch: the shadow ray of compute_light_radiance, CS:379-408
+    n_shadow++;
+    const LightRec& light = light_at(sc, ps.light);
+    const uint32_t include = __float_as_uint(light.d1.w);
+    const Hit h = shadow_intersect<STATS>(sc, ps.o, ps.d, include, ps.exclude, st);  // CS:386, 697-705
+    const float4 refl = sample_spectrum(spectra, sc.n_spectra, ps.refl, lam);
+    const float4 BRDF = make_float4(refl.x / CRT_PI_F, refl.y / CRT_PI_F, refl.z / CRT_PI_F, refl.w / CRT_PI_F);  // CS:184
+    const float cos_theta = fmaxf(0.0f, dot(ps.n, ps.d));                      // CS:388
+    const float4 spec = sample_spectrum(spectra, sc.n_spectra, __float_as_uint(light.d2.w), lam);
+    float4 le = make_float4(spec.x * cos_theta, spec.y * cos_theta, spec.z * cos_theta, spec.w * cos_theta);
+    if (h.idx == include) {
+      const Surface sh = surface_of(sc, h, ps.o, ps.d);
+      const float pdf_l = compute_light_pdf(sc, CRT_META_EMIS(sh.meta), sh.normal, sh.position, ps.o, ps.d);  // CS:393
+      const float pdf_b = cos_theta / CRT_PI_F;
+      const float w = power_heuristic(pdf_l, pdf_b);
+      le = make_float4(le.x * w / pdf_l, le.y * w / pdf_l, le.z * w / pdf_l, le.w * w / pdf_l);  // CS:400
+    } else {
+      le = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                                // CS:407
+    }
+    ps.L.x += (BRDF.x * le.x) * ps.beta.x; ps.L.y += (BRDF.y * le.y) * ps.beta.y;   // CS:187
+    ps.L.z += (BRDF.z * le.z) * ps.beta.z; ps.L.w += (BRDF.w * le.w) * ps.beta.w;
+    const float u = rnd(rng), v = rnd(rng);
+    if (STATS) st.rand_calls += 2;
+    float pdf;
+    const V3 nd = cosine_hemisphere(ps.n, u, v, pdf);                          // CS:189
+    ps.pdf = pdf;
+    const float cos_b = fabsf(dot(ps.n, nd));                                  // CS:190
+    ps.beta.x *= (BRDF.x * cos_b) / pdf; ps.beta.y *= (BRDF.y * cos_b) / pdf;  // CS:192
+    ps.beta.z *= (BRDF.z * cos_b) / pdf; ps.beta.w *= (BRDF.w * cos_b) / pdf;
+    ps.d = nd;                                                                 // origin is already the hit point
+    ps.specular = false;
+    ps.shadow_phase = false;
+  }
+  // Russian roulette, CS:279-289
+  const float rx = ps.beta.x * ps.etaScale, ry = ps.beta.y * ps.etaScale, rz = ps.beta.z * ps.etaScale;
+  const float mb = fmaxf(rx, fmaxf(ry, rz));
+  if (ps.depth > 1 && mb < 1.0f) {
+    const float q = fmaxf(0.0f, 1.0f - mb);
+    if (STATS) st.rand_calls += 1;
+    if (rnd(rng) < q) { if (STATS) term[0] = TERM_RR; return false; }
+    const float k = 1.0f - q;
+    ps.beta.x /= k; ps.beta.y /= k; ps.beta.z /= k; ps.beta.w /= k;
+  }
+  ps.depth++;                                                                  // CS:292
+  return true;
+}
+
+// seed + camera_ray + sample_wavelengths + path_trace's initial state, CS:98-101, 121-131
+template <bool STATS>
+__device__ __forceinline__ void path_begin(const DevScene& sc, uint32_t px, uint32_t py, uint32_t sample, PathState& ps, Rng& rng, Stats& st) {
+  rng.x = py; rng.y = px * 100u; rng.z = sample; rng.w = tea(px, py * 100u);   // CS:98
+  const float G = (float)sc.grid_size;
+  const float cell = (float)(sample % sc.grid_size);
+  const float s = ((float)px + (cell + rnd(rng)) / G) / (float)sc.W;            // CS:497
+  const float t = ((float)sc.H - (float)py + (cell + rnd(rng)) / G) / (float)sc.H;  // CS:498
+  const V3 eye = v3(sc.eye);
+  const V3 p = madd(madd(v3(sc.llc), s, v3(sc.hor)), t, v3(sc.ver));
+  ps.o = eye;
+  ps.d = normalize(p - eye);                                                   // CS:493
+  ps.lam0 = f2u_sat(301.0f * rnd(rng));                                        // CS:317-319
+  if (STATS) st.rand_calls += 3;
+  ps.L = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  ps.beta = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+  ps.pdf = 1.0f; ps.etaScale = 1.0f;
+  ps.exclude = CRT_MAX_U32; ps.depth = 0;
+  ps.specular = false; ps.in_transmission = false; ps.shadow_phase = false;
+}
+
+// Frames sample_start+1 .. sample_start+n_frames (UpdateVariables.wgsl:3-8 increments before each dispatch).
+//
+// Work unit = one pixel with all of this launch's frames; a lane owns its pixel for the whole launch, so
+// the accumulator is read once, the samples are added in frame order in a register (bit-identical to
+// n separate dispatches) and accumulator + framebuffer are written once.  A lane whose path ends starts
+// its next sample (or fetches its next pixel from a global counter, one atomic per warp) while the other
+// lanes of the warp keep tracing: every trip through path_step has all live lanes inside intersect().
+template <bool STATS>
+__global__ void __launch_bounds__(CRT_BLOCK) pt_megakernel(const __grid_constant__ DevScene sc, float4* __restrict__ acc, uint32_t* __restrict__ fb,
+                                                           uint32_t sample_start, uint32_t n_frames, uint32_t n_units,
+                                                           uint32_t* __restrict__ work_counter, unsigned long long* __restrict__ counters,
+                                                           uint32_t tables_in_smem) {
+  extern __shared__ float s_tables[];
+  const float* spectra = sc.spectra;
+  const float* cie = sc.cie;
+  if (tables_in_smem) {
+    const uint32_t ns = sc.n_spectra * CRT_LAMBDA_RANGE;
+    for (uint32_t i = threadIdx.x; i < ns; i += blockDim.x) s_tables[i] = sc.spectra[i];
+    for (uint32_t i = threadIdx.x; i < 3u * 471u; i += blockDim.x) s_tables[ns + i] = sc.cie[i];
+    __syncthreads();
+    spectra = s_tables;
+    cie = s_tables + ns;
+  }
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t s_end = sample_start + n_frames;
+  const bool split = (sc.shard_mode == CRT_SHARD_SPLIT_SPP && sc.world > 1);
+  const bool tiles = (sc.shard_mode == CRT_SHARD_TILES && sc.world > 1);
+
+  PathState ps;
+  Rng rng;
+  Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
+  uint32_t n_paths = 0, n_ext = 0, n_shadow = 0, depth_sum = 0;
+  uint32_t term_cnt[4] = {0, 0, 0, 0};
+  bool alive = false, have_pixel = false, exhausted = false;
+  uint32_t px = 0, py = 0, pix = 0, s_cur = 0;
+  float4 a = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+
+  for (;;) {
+    // ---- lanes between paths: next sample of the same pixel, or retire the pixel
+    if (!alive && have_pixel) {
+      uint32_t s = s_cur + 1;
+      if (split) s += (sc.rank + sc.world - ((s - 1u) % sc.world)) % sc.world;
+      if (s <= s_end) {
+        s_cur = s;
+        path_begin<STATS>(sc, px, py, s, ps, rng, st);
+        n_paths++;
+        alive = true;
+      } else {
+        acc[pix] = a;                                                          // CS:108
+        fb[pix] = resolve_pixel(a.x, a.y, a.z, s_end, sc.exposure);            // CS:109-115
+        have_pixel = false;
+      }
+    }
+    // ---- lanes without a pixel fetch one; the whole warp takes part in the ballot
+    for (;;) {
+      const bool need = !alive && !have_pixel && !exhausted;
+      const uint32_t mask = __ballot_sync(0xffffffffu, need);
+      if (mask == 0u) break;
+      uint32_t base = 0;
+      const uint32_t leader = __ffs(mask) - 1u;
+      if (lane == leader) base = atomicAdd(work_counter, (uint32_t)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (need) {
+        const uint32_t unit = base + __popc(mask & ((1u << lane) - 1u));
+        if (unit >= n_units) {
+          exhausted = true;
+        } else {
+          uint32_t tile = unit >> 5;
+          const uint32_t l = unit & 31u;
+          if (tiles) tile = tile * sc.world + sc.rank;
+          px = (tile % sc.tiles_x) * 8u + (l & 7u);
+          py = (tile / sc.tiles_x) * 4u + (l >> 3);
+          if (px < sc.W && py < sc.H) {
+            pix = px + py * sc.W;                                              // CS:107
+            a = acc[pix];
+            uint32_t s = sample_start + 1u;
+            if (split) s += (sc.rank + sc.world - ((s - 1u) % sc.world)) % sc.world;
+            have_pixel = true;
+            if (s <= s_end) {
+              s_cur = s;
+              path_begin<STATS>(sc, px, py, s, ps, rng, st);
+              n_paths++;
+              alive = true;
+            } else {
+              s_cur = s_end;   // nothing to render for this rank: retire on the next trip
+            }
+          }
+        }
+      }
+    }
+    if (__ballot_sync(0xffffffffu, alive || have_pixel) == 0u) break;
+    // ---- one intersect() per live lane
+    if (alive) {
+      uint32_t term = 0;
+      if (!path_step<STATS>(sc, spectra, ps, rng, n_ext, n_shadow, st, &term)) {
+        uint32_t lam[4];
+        wavelengths(ps.lam0, lam);
+        const V3 xyz = spectral_to_xyz(cie, ps.L, lam);                        // CS:105
+        a.x += xyz.x; a.y += xyz.y; a.z += xyz.z;                              // CS:108
+        alive = false;
+        if (STATS) { term_cnt[term - TERM_MISS]++; depth_sum += ps.depth; }
+      }
+    }
+  }
+
+  // ---- counters: one atomic per warp and counter
+  unsigned long long v[CRT_NUM_COUNTERS];
+#pragma unroll
+  for (int i = 0; i < CRT_NUM_COUNTERS; i++) v[i] = 0;
+  v[CRT_CNT_PATHS] = n_paths; v[CRT_CNT_RAYS_EXT] = n_ext; v[CRT_CNT_RAYS_SHADOW] = n_shadow;
+  if (STATS) {
+    v[CRT_CNT_PRIM_TESTS] = st.prim_tests; v[CRT_CNT_NODE_VISITS] = st.node_visits; v[CRT_CNT_TRI_TESTS] = st.tri_tests;
+    v[CRT_CNT_RAND] = st.rand_calls;
+    v[CRT_CNT_TERM_MISS] = term_cnt[0]; v[CRT_CNT_TERM_RR] = term_cnt[1]; v[CRT_CNT_TERM_LIGHT] = term_cnt[2];
+    v[CRT_CNT_TERM_DEPTH] = term_cnt[3]; v[CRT_CNT_DEPTH_SUM] = depth_sum;
+  }
+#pragma unroll
+  for (int i = 0; i < 12; i++) {
+    if (!STATS && i > CRT_CNT_RAYS_SHADOW) break;
+    unsigned long long x = v[i];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    if (lane == 0 && x) atomicAdd(&counters[i], x);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ test hook + resolve
+__global__ void trace_rays_kernel(const __grid_constant__ DevScene sc, const float4* __restrict__ rays, const uint32_t* __restrict__ exclude,
+                                  uint32_t n, uint32_t* __restrict__ hit_idx, float* __restrict__ t_out, unsigned long long* __restrict__ counters) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
+  if (i < n) {
+    const float4 o = rays[2 * i], d = rays[2 * i + 1];
+    const Hit h = intersect<true>(sc, v3(o), v3(d), exclude ? exclude[i] : CRT_MAX_U32, st);
+    hit_idx[i] = h.idx;
+    t_out[i] = h.t;
+  }
+  unsigned long long v[3] = {st.prim_tests, st.node_visits, st.tri_tests};
+  for (int k = 0; k < 3; k++) {
+    unsigned long long x = v[k];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    if ((threadIdx.x & 31u) == 0 && x) atomicAdd(&counters[CRT_CNT_PRIM_TESTS + k], x);
+  }
+}
+
+__global__ void resolve_kernel(const float4* __restrict__ acc, uint32_t* __restrict__ fb, uint32_t n, uint32_t sample, float exposure) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 a = acc[i];
+  fb[i] = resolve_pixel(a.x, a.y, a.z, sample, exposure);
+}
+
+// detmath probe: the CUDA build of include/crt_detmath.h, compared bit for bit with the oracle's build
+__global__ void detmath_kernel(const float* __restrict__ x, uint32_t n, float* s, float* c, float* e, float* p) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  crt_sincosf(x[i], &s[i], &c[i]);
+  e[i] = crt_expf(x[i]);
+  p[i] = crt_powf(x[i], 0.41666666f);
+}
+
+// ------------------------------------------------------------------------------------------------ host launchers
+namespace crt {
+
+cudaError_t launch_repack_lin(const void* prims, const uint32_t* lin_src, uint32_t n, LinPrim* out, cudaStream_t s) {
+  if (n) repack_lin_kernel<<<(n + 127) / 128, 128, 0, s>>>((const RawPrim*)prims, lin_src, n, out);
+  return cudaGetLastError();
+}
+cudaError_t launch_repack_tri(const void* prims, const uint32_t* tri_src, uint32_t n, float4* out, cudaStream_t s) {
+  if (n) repack_tri_kernel<<<(n + 127) / 128, 128, 0, s>>>((const RawPrim*)prims, tri_src, n, out);
+  return cudaGetLastError();
+}
+cudaError_t launch_repack_lights(const void* lights, uint32_t n, LightRec* out, cudaStream_t s) {
+  if (n) repack_lights_kernel<<<(n + 127) / 128, 128, 0, s>>>((const RawPrim*)lights, n, out);
+  return cudaGetLastError();
+}
+cudaError_t launch_camera_setup(const float* cam, float vph, float* out12, cudaStream_t s) {
+  camera_setup_kernel<<<1, 1, 0, s>>>(cam, vph, out12);
+  return cudaGetLastError();
+}
+
+size_t megakernel_tables_bytes(const DevScene& sc) { return ((size_t)sc.n_spectra * CRT_LAMBDA_RANGE + 3u * 471u) * sizeof(float); }
+
+cudaError_t megakernel_config(bool stats, size_t smem, int* blocks_per_sm) {
+  cudaError_t e;
+  if (stats) {
+    e = cudaFuncSetAttribute(pt_megakernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, pt_megakernel<true>, CRT_BLOCK, smem);
+  }
+  e = cudaFuncSetAttribute(pt_megakernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, pt_megakernel<false>, CRT_BLOCK, smem);
+}
+
+cudaError_t launch_megakernel(const DevScene& sc, bool stats, int grid, size_t smem, bool tables_in_smem, float4* acc, uint32_t* fb,
+                              uint32_t sample_start, uint32_t n_frames, uint32_t n_units, uint32_t* work_counter,
+                              unsigned long long* counters, cudaStream_t s) {
+  if (stats)
+    pt_megakernel<true><<<grid, CRT_BLOCK, smem, s>>>(sc, acc, fb, sample_start, n_frames, n_units, work_counter, counters, tables_in_smem ? 1u : 0u);
+  else
+    pt_megakernel<false><<<grid, CRT_BLOCK, smem, s>>>(sc, acc, fb, sample_start, n_frames, n_units, work_counter, counters, tables_in_smem ? 1u : 0u);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_trace_rays(const DevScene& sc, const float4* rays, const uint32_t* exclude, uint32_t n, uint32_t* hit_idx, float* t,
+                              unsigned long long* counters, cudaStream_t s) {
+  if (n) trace_rays_kernel<<<(n + 127) / 128, 128, 0, s>>>(sc, rays, exclude, n, hit_idx, t, counters);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_resolve(const float4* acc, uint32_t* fb, uint32_t n, uint32_t sample, float exposure, cudaStream_t s) {
+  if (n) resolve_kernel<<<(n + 255) / 256, 256, 0, s>>>(acc, fb, n, sample, exposure);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_detmath(const float* x, uint32_t n, float* sn, float* cs, float* ex, float* pw, cudaStream_t s) {
+  if (n) detmath_kernel<<<(n + 255) / 256, 256, 0, s>>>(x, n, sn, cs, ex, pw);
+  return cudaGetLastError();
+}
+
+}  // namespace crt

@@ -1,0 +1,24 @@
+// crt_kernels.h -- host-callable launchers of crt_kernels.cu
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+struct DevScene;
+struct LinPrim;
+struct LightRec;
+
+namespace crt {
+cudaError_t launch_repack_lin(const void* prims, const uint32_t* lin_src, uint32_t n, LinPrim* out, cudaStream_t s);
+cudaError_t launch_repack_tri(const void* prims, const uint32_t* tri_src, uint32_t n, float4* out, cudaStream_t s);
+cudaError_t launch_repack_lights(const void* lights, uint32_t n, LightRec* out, cudaStream_t s);
+cudaError_t launch_camera_setup(const float* cam, float vph, float* out12, cudaStream_t s);
+size_t megakernel_tables_bytes(const DevScene& sc);
+cudaError_t megakernel_config(bool stats, size_t smem, int* blocks_per_sm);
+cudaError_t launch_megakernel(const DevScene& sc, bool stats, int grid, size_t smem, bool tables_in_smem, float4* acc, uint32_t* fb,
+                              uint32_t sample_start, uint32_t n_frames, uint32_t n_units, uint32_t* work_counter,
+                              unsigned long long* counters, cudaStream_t s);
+cudaError_t launch_trace_rays(const DevScene& sc, const float4* rays, const uint32_t* exclude, uint32_t n, uint32_t* hit_idx, float* t,
+                              unsigned long long* counters, cudaStream_t s);
+cudaError_t launch_resolve(const float4* acc, uint32_t* fb, uint32_t n, uint32_t sample, float exposure, cudaStream_t s);
+cudaError_t launch_detmath(const float* x, uint32_t n, float* sn, float* cs, float* ex, float* pw, cudaStream_t s);
+}  // namespace crt

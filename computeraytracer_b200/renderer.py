@@ -1,0 +1,255 @@
+"""Host-side mirror of the reference's ``src/main.js`` over the libcrt C ABI.
+
+``Main()`` in the reference (main.js:7-624) creates the device, uploads the packed scene into
+nine bindings, and then runs ``frame()`` forever: ``sample++`` followed by one compute dispatch
+(main.js:597-611).  :class:`Renderer` is the same sequence against ``libcrt.so``:
+
+* ``Renderer(device)``            -- requestAdapter/requestDevice + pipeline (main.js:8-9, 535-543)
+* ``set_scene(packed)``           -- createBuffer/unmap of bindings 3..8 (main.js:139-393)
+* ``frame(n)``                    -- n x frame() (main.js:584-621) without the blit
+* ``accumulator()/framebuffer()`` -- readback of bindings 1 / 0 (new: the reference never reads back)
+
+The reference's host language is JavaScript; ``node`` is not available in this image, so this
+module (Python + ctypes, no torch) is the tested host layer and ``js/`` holds the N-API source a
+Node user would build.  There is no CPU fallback: importing works anywhere,
+but creating a Renderer without ``libcrt.so`` and a B200 raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+from .scene_loader import PackedScene
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcrt.so")
+
+NUM_COUNTERS = 16
+COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits", "tri_tests", "rand",
+                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum"]
+SHARD_NONE, SHARD_TILES, SHARD_SPLIT_SPP = 0, 1, 2
+KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
+
+STATUS = {0: "CRT_OK", 1: "CRT_ERR_ARG", 2: "CRT_ERR_BINDING", 3: "CRT_ERR_SIZE", 4: "CRT_ERR_STATE",
+          5: "CRT_ERR_CUDA", 6: "CRT_ERR_OOM", 7: "CRT_ERR_NODEVICE"}
+
+
+class CrtError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"{STATUS.get(code, code)}: {msg}")
+        self.code = code
+
+
+class Params(C.Structure):
+    """``struct crt_params`` (include/crt.h)."""
+    _fields_ = [("max_depth", C.c_uint32), ("grid_size", C.c_uint32), ("t_min", C.c_float), ("exposure", C.c_float),
+                ("kernel", C.c_uint32), ("frames_per_launch", C.c_uint32), ("reserved", C.c_uint32 * 6)]
+
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None) -> C.CDLL:
+    """dlopen libcrt.so and declare the prototypes of include/crt.h.  Raises if it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                                "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    vp, u32, sz = C.c_void_p, C.c_uint32, C.c_size_t
+    lib.crt_version.restype = C.c_char_p
+    lib.crt_last_error.restype = C.c_char_p
+    lib.crt_last_error.argtypes = [vp]
+    lib.crt_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.crt_destroy.argtypes = [vp]
+    lib.crt_destroy.restype = None
+    lib.crt_set_binding.argtypes = [vp, u32, vp, sz]
+    lib.crt_reset.argtypes = [vp]
+    lib.crt_default_params.argtypes = [C.POINTER(Params)]
+    lib.crt_default_params.restype = None
+    lib.crt_set_params.argtypes = [vp, C.POINTER(Params)]
+    lib.crt_get_params.argtypes = [vp, C.POINTER(Params)]
+    lib.crt_set_shard.argtypes = [vp, u32, u32, u32]
+    lib.crt_dispatch_frames.argtypes = [vp, u32]
+    lib.crt_synchronize.argtypes = [vp]
+    lib.crt_last_dispatch_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    lib.crt_read_binding.argtypes = [vp, u32, vp, sz]
+    lib.crt_resolve_framebuffer.argtypes = [vp]
+    lib.crt_device_ptr.argtypes = [vp, u32, C.POINTER(vp), C.POINTER(sz)]
+    lib.crt_stream.argtypes = [vp, C.POINTER(vp)]
+    lib.crt_trace_rays.argtypes = [vp, vp, vp, sz, vp, vp]
+    lib.crt_get_counters.argtypes = [vp, vp, sz]
+    lib.crt_reset_counters.argtypes = [vp]
+    lib.crt_scene_stats.argtypes = [vp, vp, sz]
+    lib.crt_test_detmath.argtypes = [vp, vp, sz, vp, vp, vp, vp]
+    if path == LIB_PATH:
+        _lib = lib
+    return lib
+
+
+def default_params(**kw) -> Params:
+    p = Params()
+    load_library().crt_default_params(C.byref(p))
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+class Renderer:
+    """One libcrt context on one GPU."""
+
+    def __init__(self, device: int = 0, lib: Optional[C.CDLL] = None):
+        self.lib = lib or load_library()
+        h = C.c_void_p()
+        rc = self.lib.crt_create(device, C.byref(h))
+        if rc:
+            raise CrtError(rc, f"crt_create(device={device}) failed -- libcrt needs a B200 (sm_100); there is no CPU fallback")
+        self.h = h
+        self.device = device
+        self.width = self.height = 0
+
+    # ---- lifetime
+    def close(self) -> None:
+        if getattr(self, "h", None):
+            self.lib.crt_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc: int) -> None:
+        if rc:
+            raise CrtError(rc, self.lib.crt_last_error(self.h).decode())
+
+    # ---- inputs
+    def set_binding(self, binding: int, data) -> None:
+        buf = data if isinstance(data, (bytes, bytearray)) else np.ascontiguousarray(data).tobytes()
+        self._ck(self.lib.crt_set_binding(self.h, binding, buf, len(buf)))
+
+    def set_scene(self, ps: PackedScene) -> None:
+        """Upload bindings 3..8 in the reference's layouts (main.js:139-393)."""
+        for b, data in ps.bindings().items():
+            self.set_binding(b, data)
+        self.width, self.height = int(ps.camera[11]), int(ps.camera[12])
+
+    def set_camera(self, camera16: np.ndarray) -> None:
+        cam = np.ascontiguousarray(camera16, dtype="<f4")
+        self.set_binding(4, cam)
+        self.width, self.height = int(cam[11]), int(cam[12])
+
+    def set_params(self, params: Optional[Params] = None, **kw) -> Params:
+        p = params or self.get_params()
+        for k, v in kw.items():
+            setattr(p, k, v)
+        self._ck(self.lib.crt_set_params(self.h, C.byref(p)))
+        return p
+
+    def get_params(self) -> Params:
+        p = Params()
+        self._ck(self.lib.crt_get_params(self.h, C.byref(p)))
+        return p
+
+    def enable_stats(self, on: bool = True) -> None:
+        """Detailed device counters (primitive tests, node visits, rand calls, termination mix)."""
+        p = self.get_params()
+        p.reserved[0] = (p.reserved[0] | 1) if on else (p.reserved[0] & ~1)
+        self._ck(self.lib.crt_set_params(self.h, C.byref(p)))
+
+    def set_shard(self, rank: int, world: int, mode: int) -> None:
+        self._ck(self.lib.crt_set_shard(self.h, rank, world, mode))
+
+    def reset(self) -> None:
+        self._ck(self.lib.crt_reset(self.h))
+
+    # ---- the frame loop
+    def frame(self, n: int = 1) -> None:
+        """n x frame() of main.js:584-621 (sample++ then one sample per pixel); asynchronous."""
+        self._ck(self.lib.crt_dispatch_frames(self.h, n))
+
+    def synchronize(self) -> None:
+        self._ck(self.lib.crt_synchronize(self.h))
+
+    def last_dispatch_ms(self) -> float:
+        ms = C.c_float()
+        self._ck(self.lib.crt_last_dispatch_ms(self.h, C.byref(ms)))
+        return float(ms.value)
+
+    # ---- outputs
+    @property
+    def sample(self) -> int:
+        v = C.c_uint32()
+        self._ck(self.lib.crt_read_binding(self.h, 2, C.byref(v), 4))
+        return int(v.value)
+
+    def accumulator(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        """Binding 1: float32[H, W, 4] XYZ sums (lane 3 is padding)."""
+        if out is None:
+            out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        self._ck(self.lib.crt_read_binding(self.h, 1, out.ctypes.data, out.nbytes))
+        return out
+
+    def framebuffer(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        """Binding 0: uint8[H, W, 4] RGBA, top-left origin."""
+        if out is None:
+            out = np.empty((self.height, self.width, 4), dtype=np.uint8)
+        self._ck(self.lib.crt_read_binding(self.h, 0, out.ctypes.data, out.nbytes))
+        return out
+
+    def resolve_framebuffer(self) -> None:
+        self._ck(self.lib.crt_resolve_framebuffer(self.h))
+
+    def device_ptr(self, binding: int):
+        p, n = C.c_void_p(), C.c_size_t()
+        self._ck(self.lib.crt_device_ptr(self.h, binding, C.byref(p), C.byref(n)))
+        return int(p.value), int(n.value)
+
+    def stream(self) -> int:
+        s = C.c_void_p()
+        self._ck(self.lib.crt_stream(self.h, C.byref(s)))
+        return int(s.value or 0)
+
+    # ---- hooks
+    def trace_rays(self, rays: np.ndarray, exclude: Optional[np.ndarray] = None):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        n = rays.shape[0]
+        idx = np.empty(n, dtype=np.uint32)
+        t = np.empty(n, dtype=np.float32)
+        ex = None if exclude is None else np.ascontiguousarray(exclude, dtype=np.uint32)
+        self._ck(self.lib.crt_trace_rays(self.h, rays.ctypes.data, ex.ctypes.data if ex is not None else None, n,
+                                         idx.ctypes.data, t.ctypes.data))
+        return idx, t
+
+    def counters(self) -> dict:
+        out = np.zeros(NUM_COUNTERS, dtype=np.uint64)
+        self._ck(self.lib.crt_get_counters(self.h, out.ctypes.data, NUM_COUNTERS))
+        return {k: int(out[i]) for i, k in enumerate(COUNTER_NAMES)}
+
+    def reset_counters(self) -> None:
+        self._ck(self.lib.crt_reset_counters(self.h))
+
+    def scene_stats(self) -> dict:
+        out = np.zeros(8, dtype=np.uint64)
+        self._ck(self.lib.crt_scene_stats(self.h, out.ctypes.data, 8))
+        keys = ["n_prims", "n_linear", "n_triangles", "bvh_nodes", "bvh_bytes", "tri_bytes", "build_us", "bvh_depth"]
+        return {k: int(out[i]) for i, k in enumerate(keys)}
+
+    def test_detmath(self, x: np.ndarray):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        outs = [np.empty_like(x) for _ in range(4)]
+        self._ck(self.lib.crt_test_detmath(self.h, x.ctypes.data, x.size, *[o.ctypes.data for o in outs]))
+        return outs

@@ -153,6 +153,11 @@ CRT_API int crt_reset_counters(crt_ctx* ctx);
  * [7]=max BVH depth. */
 CRT_API int crt_scene_stats(crt_ctx* ctx, uint64_t* out, size_t n);
 
+/* Test hook: the CUDA build of crt_detmath.h (sin, cos, exp, pow(x, 1/2.4)) on n inputs, compared bit
+ * for bit with the oracle's gcc build of the same header. */
+CRT_API int crt_test_detmath(crt_ctx* ctx, const float* x, size_t n, float* sin_out, float* cos_out,
+                             float* exp_out, float* pow_out);
+
 CRT_API const char* crt_last_error(crt_ctx* ctx);
 CRT_API const char* crt_version(void);
 
