@@ -25,6 +25,8 @@ struct crt_ctx {
   int device = 0;
   int sm_count = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t own_stream = nullptr;
+  uint64_t launches = 0;   // hot-path kernel launches since the last crt_reset_counters
   cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
   bool timed = false;
   std::string err;
@@ -275,13 +277,14 @@ int crt_create(int device, crt_ctx** out) {
   ctx->sm_count = prop.multiProcessorCount;
   crt_default_params(&ctx->params);
   memset(&ctx->scene, 0, sizeof(ctx->scene));
-  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&ctx->ev_start) != cudaSuccess || cudaEventCreate(&ctx->ev_stop) != cudaSuccess ||
       cudaMalloc(&ctx->d_work, 4) != cudaSuccess || cudaMalloc(&ctx->d_counters, CRT_NUM_COUNTERS * 8) != cudaSuccess ||
       cudaMemset(ctx->d_counters, 0, CRT_NUM_COUNTERS * 8) != cudaSuccess) {
     crt_destroy(ctx);
     return CRT_ERR_CUDA;
   }
+  ctx->stream = ctx->own_stream;
   *out = ctx;
   return CRT_OK;
 }
@@ -294,7 +297,7 @@ void crt_destroy(crt_ctx* ctx) {
   dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_tri); dfree(ctx->d_nodes); dfree(ctx->d_work); dfree(ctx->d_counters);
   if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
   if (ctx->ev_stop) cudaEventDestroy(ctx->ev_stop);
-  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
 
@@ -408,6 +411,7 @@ int crt_dispatch_frames(crt_ctx* ctx, uint32_t n) {
     CU(crt::launch_megakernel(s, stats, grid, smem, tables_in_smem, ctx->d_acc, ctx->d_fb, ctx->sample, k, n_units, ctx->d_work,
                               ctx->d_counters, ctx->stream));
     ctx->sample += k;   // UpdateVariables.wgsl:3-8, once per frame
+    ctx->launches++;
     left -= k;
   }
   CU(cudaEventRecord(ctx->ev_stop, ctx->stream));
@@ -469,6 +473,14 @@ int crt_device_ptr(crt_ctx* ctx, uint32_t binding, void** dptr, size_t* nbytes) 
   return CRT_OK;
 }
 
+int crt_set_stream(crt_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return CRT_ERR_ARG;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+  return CRT_OK;
+}
+
 int crt_stream(crt_ctx* ctx, void** cuda_stream) {
   if (!ctx || !cuda_stream) return CRT_ERR_ARG;
   *cuda_stream = (void*)ctx->stream;
@@ -506,6 +518,7 @@ int crt_get_counters(crt_ctx* ctx, uint64_t* out, size_t n) {
   unsigned long long tmp[CRT_NUM_COUNTERS];
   CU(cudaMemcpyAsync(tmp, ctx->d_counters, sizeof(tmp), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
+  tmp[CRT_CNT_LAUNCHES] = ctx->launches;
   for (size_t i = 0; i < n; i++) out[i] = tmp[i];
   return CRT_OK;
 }
@@ -514,6 +527,7 @@ int crt_reset_counters(crt_ctx* ctx) {
   if (!ctx) return CRT_ERR_ARG;
   CU(cudaSetDevice(ctx->device));
   CU(cudaMemsetAsync(ctx->d_counters, 0, CRT_NUM_COUNTERS * 8, ctx->stream));
+  ctx->launches = 0;
   return CRT_OK;
 }
 

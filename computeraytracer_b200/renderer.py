@@ -29,7 +29,7 @@ LIB_PATH = os.path.join(_HERE, "libcrt.so")
 
 NUM_COUNTERS = 16
 COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits", "tri_tests", "rand",
-                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum"]
+                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum", "launches"]
 SHARD_NONE, SHARD_TILES, SHARD_SPLIT_SPP = 0, 1, 2
 KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
 
@@ -83,6 +83,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.crt_resolve_framebuffer.argtypes = [vp]
     lib.crt_device_ptr.argtypes = [vp, u32, C.POINTER(vp), C.POINTER(sz)]
     lib.crt_stream.argtypes = [vp, C.POINTER(vp)]
+    lib.crt_set_stream.argtypes = [vp, vp]
     lib.crt_trace_rays.argtypes = [vp, vp, vp, sz, vp, vp]
     lib.crt_get_counters.argtypes = [vp, vp, sz]
     lib.crt_reset_counters.argtypes = [vp]
@@ -222,6 +223,10 @@ class Renderer:
         s = C.c_void_p()
         self._ck(self.lib.crt_stream(self.h, C.byref(s)))
         return int(s.value or 0)
+
+    def set_stream(self, cuda_stream: int) -> None:
+        """Launch on a caller-owned CUDA stream (0/None: the context's own)."""
+        self._ck(self.lib.crt_set_stream(self.h, C.c_void_p(cuda_stream or None)))
 
     # ---- hooks
     def trace_rays(self, rays: np.ndarray, exclude: Optional[np.ndarray] = None):

@@ -89,7 +89,8 @@ enum crt_counter {
   CRT_CNT_TERM_RR = 8,
   CRT_CNT_TERM_LIGHT = 9,
   CRT_CNT_TERM_DEPTH = 10,
-  CRT_CNT_DEPTH_SUM = 11    /* sum over paths of depth at termination                     */
+  CRT_CNT_DEPTH_SUM = 11,   /* sum over paths of depth at termination                     */
+  CRT_CNT_LAUNCHES = 12     /* hot-path kernel launches (counted on the host)             */
 };
 
 /* requestAdapter/requestDevice + pipeline creation (MJ:8-9, MJ:535-543).  Fails with
@@ -136,6 +137,9 @@ CRT_API int crt_resolve_framebuffer(crt_ctx* ctx);
  * (reduce / gather over NVLink) without a copy.  Also the CUDA stream the context launches on. */
 CRT_API int crt_device_ptr(crt_ctx* ctx, uint32_t binding, void** dptr, size_t* nbytes);
 CRT_API int crt_stream(crt_ctx* ctx, void** cuda_stream);
+/* Launch on a caller-owned CUDA stream (NULL: back to the context's own), e.g. the host layer's
+ * current stream so that its events bracket the kernels. */
+CRT_API int crt_set_stream(crt_ctx* ctx, void* cuda_stream);
 
 /* Test hook: closest hit of intersect() (CS:503-518) for n caller-supplied rays.
  * rays: n x 8 floats (origin.xyz, unused, direction.xyz, unused).  exclude: n primitive

@@ -91,7 +91,7 @@ class OracleScene:
     def __init__(self, orc: Oracle, ps, params: Params, use_bvh: bool):
         self.orc = orc
         self.lib = orc.lib
-        self.params = params
+        self.params = Params.from_buffer_copy(bytes(params))   # accepts the product's Params struct too (same layout)
         self.W, self.H = int(ps.camera[11]), int(ps.camera[12])
         self._prims = np.frombuffer(ps.primitives.tobytes(), dtype=np.uint8).copy()
         self._lights = np.frombuffer(ps.lights.tobytes(), dtype=np.uint8).copy()
