@@ -5,6 +5,7 @@
 // There is no CPU fallback: without a usable sm_100 device crt_create fails.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -18,6 +19,7 @@
 #include "crt_bvh.h"
 #include "crt_device.cuh"
 #include "crt_kernels.h"
+#include "crt_wavefront.h"
 
 #define CRT_VERSION_STRING "libcrt 0.1 (sm_100a)"
 
@@ -54,6 +56,16 @@ struct crt_ctx {
   DevScene scene;
   uint64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   std::vector<uint8_t> pending_acc;  // binding 1 set before the size is known
+
+  // wavefront path (crt_wavefront.cu)
+  WfState wf;
+  void* wf_mem = nullptr;            // one allocation behind all WfState arrays
+  uint32_t wf_slots = 0;
+  uint32_t* wf_host_count = nullptr; // pinned: live-slot count read back at check points
+  void* wf_stage = nullptr;          // per-sample XYZ staging of the current chunk
+  size_t wf_stage_bytes = 0;
+  uint32_t wf_last_iters = 0;        // iterations the previous chunk needed (predicts the next check point)
+  uint64_t wf_iterations = 0;
 };
 
 namespace {
@@ -167,6 +179,7 @@ int upload_scene(crt_ctx* ctx) {
   DevScene& s = ctx->scene;
   s.n_lin = (uint32_t)lin_pos.size(); s.n_tri = (uint32_t)tri_pos.size(); s.n_nodes = bvh.n_nodes; s.n_lights = (uint32_t)n_lights;
   s.lin_g = nullptr; s.tri = nullptr; s.nodes = nullptr; s.lights_g = nullptr;
+  for (int a = 0; a < 3; a++) { s.bvh_lo[a] = bvh.lo[a]; s.bvh_hi[a] = bvh.hi[a]; }
 
   void* d_lights_raw = nullptr; uint32_t* d_src = nullptr;
   if (n_prims) {
@@ -237,6 +250,117 @@ int prepare(crt_ctx* ctx) {
   return CRT_OK;
 }
 
+int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
+  if (ctx->wf_mem && ctx->wf_slots >= n_slots) return CRT_OK;
+  if (ctx->wf_mem) { cudaFree(ctx->wf_mem); ctx->wf_mem = nullptr; }
+  const size_t cnt_bytes = (size_t)(3 * CRT_WF_MAX_ITERS + 4) * 4;
+  const size_t total = (size_t)(8 * 16 + 3 * 4) * n_slots + cnt_bytes + 256;   // S0..S6, H; two live lists and the BVH queue
+  CU(cudaMalloc(&ctx->wf_mem, total));
+  uint8_t* p = (uint8_t*)ctx->wf_mem;
+  WfState& w = ctx->wf;
+  w.S0 = (float4*)p; p += 16 * (size_t)n_slots;
+  w.S1 = (float4*)p; p += 16 * (size_t)n_slots;
+  w.S2 = (float4*)p; p += 16 * (size_t)n_slots;
+  w.S3 = (float4*)p; p += 16 * (size_t)n_slots;
+  w.S4 = (uint4*)p; p += 16 * (size_t)n_slots;
+  w.S5 = (uint4*)p; p += 16 * (size_t)n_slots;
+  w.S6 = (float4*)p; p += 16 * (size_t)n_slots;
+  w.H = (float4*)p; p += 16 * (size_t)n_slots;
+  w.list[0] = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.list[1] = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.bvh_list = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.n_active = (uint32_t*)p; p += 4 * (size_t)(CRT_WF_MAX_ITERS + 4);
+  w.n_bvh = (uint32_t*)p; p += 4 * (size_t)CRT_WF_MAX_ITERS;
+  w.n_fetch = (uint32_t*)p;
+  ctx->wf_slots = n_slots;
+  if (!ctx->wf_host_count) CU(cudaMallocHost(&ctx->wf_host_count, 4));
+  return CRT_OK;
+}
+
+// n frames as a wavefront, in chunks.  Per iteration one wf_logic launch (+ one wf_traverse launch when the
+// scene has triangles); a chunk's loop ends when a check point reads back zero live slots; wf_accumulate then
+// adds the chunk's samples to binding 1 in frame order and rebuilds binding 0.
+int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
+  const DevScene& s = ctx->scene;
+  size_t smem = crt::wf_tables_bytes(s);
+  ctx->wf.tables_in_smem = smem <= 48 * 1024 ? 1u : 0u;
+  if (!ctx->wf.tables_in_smem) smem = 0;
+  int bl = 0, bt = 0;
+  CU(crt::wf_config(stats, smem, &bl, &bt));
+  if (bl < 1 || bt < 1) return fail(ctx, CRT_ERR_CUDA, "wavefront kernels do not fit on an SM");
+  const int grid_l = ctx->sm_count * bl, grid_t = ctx->sm_count * bt;
+  // a path needs at most 2*(max_depth+1)+1 rays; keep a chunk's worst case inside the counter arrays
+  const uint64_t worst = 2ull * ((uint64_t)ctx->params.max_depth + 2ull);
+  if (worst + 2 > CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_ARG, "max_depth %u is too deep for the wavefront kernel; use CRT_KERNEL_MEGA", ctx->params.max_depth);
+  uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 32u;
+  uint32_t lanes_max = ctx->params.reserved[1] ? ctx->params.reserved[1] : 8u;   // reserved[1]: concurrent samples per pixel
+  const size_t n_pixels = ctx->acc_pixels;
+  // memory guards: path state <= ~6 GB, staging <= ~4 GB
+  while (lanes_max > 1 && (uint64_t)n_units * lanes_max * 140ull > (6ull << 30)) lanes_max--;
+  while (chunk > 1 && (uint64_t)n_pixels * chunk * 16ull > (4ull << 30)) chunk--;
+  const size_t cnt_bytes = (size_t)(3 * CRT_WF_MAX_ITERS + 4) * 4;
+  const bool split = ctx->shard_mode == CRT_SHARD_SPLIT_SPP && ctx->world > 1;
+  uint32_t left = n;
+  while (left) {
+    const uint32_t k = left < chunk ? left : chunk;
+    WfChunk ck;
+    ck.n_units = n_units; ck.n_pixels = (uint32_t)n_pixels;
+    if (split) {
+      uint32_t first = ctx->sample + 1u;
+      first += (ctx->rank + ctx->world - ((first - 1u) % ctx->world)) % ctx->world;
+      const uint32_t end = ctx->sample + k;
+      ck.s_first = first; ck.s_stride = ctx->world;
+      ck.n_samples = first <= end ? (end - first) / ctx->world + 1u : 0u;
+    } else {
+      ck.s_first = ctx->sample + 1u; ck.s_stride = 1u; ck.n_samples = k;
+    }
+    ck.lanes = std::max(1u, std::min(lanes_max, ck.n_samples));
+    const uint64_t iters_worst = worst * ((ck.n_samples + ck.lanes - 1) / ck.lanes) + 2;
+    if (iters_worst > CRT_WF_MAX_ITERS) {   // shrink the chunk so the per-iteration counters cannot run out
+      const uint32_t per_lane = (uint32_t)std::max<uint64_t>(1, (CRT_WF_MAX_ITERS - 2) / worst);
+      chunk = std::max(1u, per_lane * ck.lanes / (split ? ctx->world : 1u));
+      if (chunk < k) continue;
+    }
+    const size_t stage_bytes = (size_t)std::max(1u, ck.n_samples) * n_pixels * 16;
+    if (stage_bytes > ctx->wf_stage_bytes) {
+      if (ctx->wf_stage) { cudaFree(ctx->wf_stage); ctx->wf_stage = nullptr; ctx->wf_stage_bytes = 0; }
+      CU(cudaMalloc(&ctx->wf_stage, stage_bytes));
+      ctx->wf_stage_bytes = stage_bytes;
+    }
+    ck.stage = (float4*)ctx->wf_stage;
+    if (ck.n_samples && n_units) {
+      int rc = ensure_wavefront(ctx, n_units * ck.lanes);
+      if (rc) return rc;
+      CU(cudaMemsetAsync(ctx->wf.n_active, 0, cnt_bytes, ctx->stream));
+      uint32_t it = 0;
+      uint32_t next_check = ctx->wf_last_iters > 4 ? ctx->wf_last_iters - 1 : 2 * ((ck.n_samples + ck.lanes - 1) / ck.lanes) + 1;
+      for (;;) {
+        CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, grid_l, smem, it, ctx->d_counters, ctx->stream));
+        ctx->launches++;
+        if (s.n_tri) {
+          CU(crt::launch_wf_traverse(s, ctx->wf, stats, grid_t, it, ctx->d_counters, ctx->stream));
+          ctx->launches++;
+        }
+        it++;
+        if (it >= next_check) {
+          CU(cudaMemcpyAsync(ctx->wf_host_count, ctx->wf.n_active + it, 4, cudaMemcpyDeviceToHost, ctx->stream));
+          CU(cudaStreamSynchronize(ctx->stream));
+          if (*ctx->wf_host_count == 0) break;
+          next_check = it + 4;
+        }
+        if (it + 2 >= CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_STATE, "wavefront iteration limit reached");
+      }
+      ctx->wf_last_iters = it;
+      ctx->wf_iterations += it;
+    }
+    ctx->sample += k;   // UpdateVariables.wgsl:3-8, once per frame
+    CU(crt::launch_wf_accumulate(s, ck, ctx->d_acc, ctx->d_fb, ctx->sample, ctx->stream));
+    ctx->launches++;
+    left -= k;
+  }
+  return CRT_OK;
+}
+
 size_t binding_bytes(const crt_ctx* ctx, uint32_t binding) {
   switch (binding) {
     case 0: return (size_t)ctx->W * ctx->H * 4;
@@ -277,6 +401,7 @@ int crt_create(int device, crt_ctx** out) {
   ctx->sm_count = prop.multiProcessorCount;
   crt_default_params(&ctx->params);
   memset(&ctx->scene, 0, sizeof(ctx->scene));
+  memset(&ctx->wf, 0, sizeof(ctx->wf));
   if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&ctx->ev_start) != cudaSuccess || cudaEventCreate(&ctx->ev_stop) != cudaSuccess ||
       cudaMalloc(&ctx->d_work, 4) != cudaSuccess || cudaMalloc(&ctx->d_counters, CRT_NUM_COUNTERS * 8) != cudaSuccess ||
@@ -295,6 +420,9 @@ void crt_destroy(crt_ctx* ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   dfree(ctx->d_acc); dfree(ctx->d_fb); dfree(ctx->d_spectra); dfree(ctx->d_cie); dfree(ctx->d_prims_raw);
   dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_tri); dfree(ctx->d_nodes); dfree(ctx->d_work); dfree(ctx->d_counters);
+  if (ctx->wf_mem) cudaFree(ctx->wf_mem);
+  if (ctx->wf_stage) cudaFree(ctx->wf_stage);
+  if (ctx->wf_host_count) cudaFreeHost(ctx->wf_host_count);
   if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
   if (ctx->ev_stop) cudaEventDestroy(ctx->ev_stop);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -391,28 +519,36 @@ int crt_dispatch_frames(crt_ctx* ctx, uint32_t n) {
   if (n > 0xFFFFFFFFu - ctx->sample) return fail(ctx, CRT_ERR_ARG, "frame counter would overflow");
   const DevScene& s = ctx->scene;
   const bool stats = (ctx->params.reserved[0] & 1u) != 0;   // reserved[0] bit 0: detailed device counters
-  size_t smem = crt::megakernel_tables_bytes(s);
-  bool tables_in_smem = smem <= 48 * 1024;
-  if (!tables_in_smem) smem = 0;
-  int bps = 0;
-  CU(crt::megakernel_config(stats, smem, &bps));
-  if (bps < 1) return fail(ctx, CRT_ERR_CUDA, "megakernel does not fit on an SM");
-  const int grid = ctx->sm_count * bps;
   uint32_t n_tiles = s.tiles_x * s.tiles_y;
   if (ctx->shard_mode == CRT_SHARD_TILES && ctx->world > 1)
     n_tiles = (n_tiles > ctx->rank) ? (n_tiles - ctx->rank + ctx->world - 1) / ctx->world : 0;
   const uint32_t n_units = n_tiles * 32u;
-  uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 8u;
+  // AUTO: the wavefront form when there is a BVH (ncu: the megakernel runs 4.75 of 32 lanes there), the
+  // megakernel for linear-list-only scenes (all lanes share the same primitive loop)
+  uint32_t kernel = ctx->params.kernel;
+  if (kernel == CRT_KERNEL_AUTO) kernel = (s.n_tri > 0 && ctx->params.max_depth <= 1000) ? CRT_KERNEL_WAVEFRONT : CRT_KERNEL_MEGA;
   CU(cudaEventRecord(ctx->ev_start, ctx->stream));
-  uint32_t left = n;
-  while (left) {
-    const uint32_t k = left < chunk ? left : chunk;
-    CU(cudaMemsetAsync(ctx->d_work, 0, 4, ctx->stream));
-    CU(crt::launch_megakernel(s, stats, grid, smem, tables_in_smem, ctx->d_acc, ctx->d_fb, ctx->sample, k, n_units, ctx->d_work,
-                              ctx->d_counters, ctx->stream));
-    ctx->sample += k;   // UpdateVariables.wgsl:3-8, once per frame
-    ctx->launches++;
-    left -= k;
+  if (kernel == CRT_KERNEL_WAVEFRONT) {
+    if (n) { rc = dispatch_wavefront(ctx, n, n_units, stats); if (rc) return rc; }
+  } else {
+    size_t smem = crt::megakernel_tables_bytes(s);
+    bool tables_in_smem = smem <= 48 * 1024;
+    if (!tables_in_smem) smem = 0;
+    int bps = 0;
+    CU(crt::megakernel_config(stats, smem, &bps));
+    if (bps < 1) return fail(ctx, CRT_ERR_CUDA, "megakernel does not fit on an SM");
+    const int grid = ctx->sm_count * bps;
+    uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 8u;
+    uint32_t left = n;
+    while (left) {
+      const uint32_t k = left < chunk ? left : chunk;
+      CU(cudaMemsetAsync(ctx->d_work, 0, 4, ctx->stream));
+      CU(crt::launch_megakernel(s, stats, grid, smem, tables_in_smem, ctx->d_acc, ctx->d_fb, ctx->sample, k, n_units, ctx->d_work,
+                                ctx->d_counters, ctx->stream));
+      ctx->sample += k;   // UpdateVariables.wgsl:3-8, once per frame
+      ctx->launches++;
+      left -= k;
+    }
   }
   CU(cudaEventRecord(ctx->ev_stop, ctx->stream));
   ctx->timed = true;
@@ -519,6 +655,7 @@ int crt_get_counters(crt_ctx* ctx, uint64_t* out, size_t n) {
   CU(cudaMemcpyAsync(tmp, ctx->d_counters, sizeof(tmp), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   tmp[CRT_CNT_LAUNCHES] = ctx->launches;
+  tmp[CRT_CNT_WF_ITERATIONS] = ctx->wf_iterations;
   for (size_t i = 0; i < n; i++) out[i] = tmp[i];
   return CRT_OK;
 }
@@ -528,6 +665,7 @@ int crt_reset_counters(crt_ctx* ctx) {
   CU(cudaSetDevice(ctx->device));
   CU(cudaMemsetAsync(ctx->d_counters, 0, CRT_NUM_COUNTERS * 8, ctx->stream));
   ctx->launches = 0;
+  ctx->wf_iterations = 0;
   return CRT_OK;
 }
 

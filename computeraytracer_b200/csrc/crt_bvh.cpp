@@ -171,6 +171,7 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
   const float ext = std::max(scene.hi[0] - scene.lo[0], std::max(scene.hi[1] - scene.lo[1], scene.hi[2] - scene.lo[2]));
   const float pad = std::max(ext, 1.0f) * (1.0f / 32768.0f);
   out.pad = pad;
+  for (int a = 0; a < 3; a++) { out.lo[a] = scene.lo[a] - pad; out.hi[a] = scene.hi[a] + pad; }
 
   Builder b(items, n_threads < 1 ? 1 : n_threads);
   b.build(0, 0, (uint32_t)n, 0);

@@ -11,6 +11,7 @@ struct BvhResult {
   uint32_t n_nodes = 0;
   uint32_t max_depth = 0;
   float pad = 0.0f;
+  float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};   // padded bounds of all triangles
 };
 
 // prims: binding-8 bytes (80-byte records); tri_pos: positions of the category-2 records.

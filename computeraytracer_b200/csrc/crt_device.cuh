@@ -68,6 +68,7 @@ struct DevScene {
   const float4* tri;              // 3 x float4 per triangle, BVH leaf order
   const float4* nodes;            // 4 x float4 per BVH2 node
   uint32_t shadow_closest;        // 1: some light's primitive is a triangle -> shadow rays need closest-hit
+  float bvh_lo[3], bvh_hi[3];     // padded bounds of all triangles (root box)
   // sharding
   uint32_t rank, world, shard_mode;
   uint32_t tiles_x, tiles_y;
@@ -190,6 +191,77 @@ __device__ __forceinline__ bool test_tri(float4 T0, float4 T1, float4 T2, V3 o, 
 // Boxes are padded at build time so that culling with (tnear <= best.t) never drops a primitive the
 // linear scan would accept (DESIGN.md "Conservative culling"); equal-t ties go to the higher
 // primitive index, which is what the reference's in-order scan with `t > t_max` rejection yields.
+// Inner-node step: test both children, descend into the nearer one, push the other.  On return `node` is
+// the next node to process (inner >= 0, leaf < 0); returns false when nothing is left (stack empty).
+template <bool STATS>
+__device__ __forceinline__ bool trav_inner(const float4* __restrict__ nodes, V3 o, float idx, float idy, float idz, float t_min,
+                                           const Hit& h, int& node, int& sp, int* stack, Stats& st) {
+  const float4 n0 = __ldg(&nodes[4 * node + 0]);
+  const float4 n1 = __ldg(&nodes[4 * node + 1]);
+  const float4 n2 = __ldg(&nodes[4 * node + 2]);
+  const float4 n3 = __ldg(&nodes[4 * node + 3]);
+  if (STATS) st.node_visits++;
+  float a0 = (n0.x - o.x) * idx, a1 = (n0.y - o.x) * idx;
+  float b0 = (n0.z - o.y) * idy, b1 = (n0.w - o.y) * idy;
+  float c0 = (n2.x - o.z) * idz, c1 = (n2.y - o.z) * idz;
+  const float tn0 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), t_min));
+  const float tf0 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), h.t));
+  a0 = (n1.x - o.x) * idx; a1 = (n1.y - o.x) * idx;
+  b0 = (n1.z - o.y) * idy; b1 = (n1.w - o.y) * idy;
+  c0 = (n2.z - o.z) * idz; c1 = (n2.w - o.z) * idz;
+  const float tn1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), t_min));
+  const float tf1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), h.t));
+  const bool hit0 = tn0 <= tf0, hit1 = tn1 <= tf1;
+  const int ch0 = __float_as_int(n3.x), ch1 = __float_as_int(n3.y);
+  if (hit0 && hit1) {
+    const bool swap = tn1 < tn0;
+    node = swap ? ch1 : ch0;
+    stack[sp++] = swap ? ch0 : ch1;
+    return true;
+  }
+  if (hit0) { node = ch0; return true; }
+  if (hit1) { node = ch1; return true; }
+  if (sp == 0) return false;
+  node = stack[--sp];
+  return true;
+}
+
+// Leaf step: test the leaf's triangles under the tie rule.  Returns false when the traversal is over
+// (stack empty, or an any-hit query found its occluder); otherwise `node` is the next node.
+template <bool STATS>
+__device__ __forceinline__ bool trav_leaf(const float4* __restrict__ tris, V3 o, V3 d, uint32_t exclude, float t_min, bool anyhit,
+                                          Hit& h, int& node, int& sp, int* stack, Stats& st) {
+  const uint32_t leaf = (uint32_t)(~node);
+  const uint32_t first = leaf >> 3, count = (leaf & 7u) + 1u;
+  for (uint32_t i = 0; i < count; i++) {
+    const uint32_t slot = first + i;
+    const float4 T0 = __ldg(&tris[3 * slot + 0]);
+    const float4 T1 = __ldg(&tris[3 * slot + 1]);
+    const float4 T2 = __ldg(&tris[3 * slot + 2]);
+    if (STATS) st.tri_tests++;
+    const uint32_t index = __float_as_uint(T0.w);
+    if (index == exclude) continue;
+    float t;
+    if (test_tri(T0, T1, T2, o, d, t_min, h.t, t)) {
+      if (t < h.t || h.idx == CRT_MAX_U32 || index > h.idx) {
+        h.t = t; h.idx = index; h.ref = CRT_TRI_REF | slot;
+        if (anyhit) return false;
+      }
+    }
+  }
+  if (sp == 0) return false;
+  node = stack[--sp];
+  return true;
+}
+
+template <bool STATS>
+__device__ __forceinline__ bool trav_step(const float4* __restrict__ nodes, const float4* __restrict__ tris, V3 o, V3 d,
+                                          float idx, float idy, float idz, uint32_t exclude, float t_min, bool anyhit,
+                                          Hit& h, int& node, int& sp, int* stack, Stats& st) {
+  if (node >= 0) return trav_inner<STATS>(nodes, o, idx, idy, idz, t_min, h, node, sp, stack, st);
+  return trav_leaf<STATS>(tris, o, d, exclude, t_min, anyhit, h, node, sp, stack, st);
+}
+
 template <bool ANYHIT, bool STATS>
 __device__ __forceinline__ void traverse(const DevScene& sc, V3 o, V3 d, uint32_t exclude, float t_min, Hit& h, Stats& st) {
   if (sc.n_tri == 0) return;
@@ -197,72 +269,36 @@ __device__ __forceinline__ void traverse(const DevScene& sc, V3 o, V3 d, uint32_
   int stack[CRT_BVH_STACK];
   int sp = 0;
   int node = 0;   // root is always an inner node (a lone leaf is wrapped at build time)
-  const float4* __restrict__ nodes = sc.nodes;
-  const float4* __restrict__ tris = sc.tri;
-  for (;;) {
-    if (node >= 0) {
-      const float4 n0 = __ldg(&nodes[4 * node + 0]);
-      const float4 n1 = __ldg(&nodes[4 * node + 1]);
-      const float4 n2 = __ldg(&nodes[4 * node + 2]);
-      const float4 n3 = __ldg(&nodes[4 * node + 3]);
-      if (STATS) st.node_visits++;
-      float a0 = (n0.x - o.x) * idx, a1 = (n0.y - o.x) * idx;
-      float b0 = (n0.z - o.y) * idy, b1 = (n0.w - o.y) * idy;
-      float c0 = (n2.x - o.z) * idz, c1 = (n2.y - o.z) * idz;
-      float tn0 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), t_min));
-      float tf0 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), h.t));
-      a0 = (n1.x - o.x) * idx; a1 = (n1.y - o.x) * idx;
-      b0 = (n1.z - o.y) * idy; b1 = (n1.w - o.y) * idy;
-      c0 = (n2.z - o.z) * idz; c1 = (n2.w - o.z) * idz;
-      float tn1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), t_min));
-      float tf1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), h.t));
-      const bool hit0 = tn0 <= tf0, hit1 = tn1 <= tf1;
-      const int ch0 = __float_as_int(n3.x), ch1 = __float_as_int(n3.y);
-      if (hit0 && hit1) {
-        const bool swap = tn1 < tn0;
-        node = swap ? ch1 : ch0;
-        stack[sp++] = swap ? ch0 : ch1;
-      } else if (hit0) {
-        node = ch0;
-      } else if (hit1) {
-        node = ch1;
-      } else {
-        if (sp == 0) return;
-        node = stack[--sp];
-      }
-    } else {
-      const uint32_t leaf = (uint32_t)(~node);
-      const uint32_t first = leaf >> 3, count = (leaf & 7u) + 1u;
-      for (uint32_t i = 0; i < count; i++) {
-        const uint32_t slot = first + i;
-        const float4 T0 = __ldg(&tris[3 * slot + 0]);
-        const float4 T1 = __ldg(&tris[3 * slot + 1]);
-        const float4 T2 = __ldg(&tris[3 * slot + 2]);
-        if (STATS) st.tri_tests++;
-        const uint32_t index = __float_as_uint(T0.w);
-        if (index == exclude) continue;
-        float t;
-        if (test_tri(T0, T1, T2, o, d, t_min, h.t, t)) {
-          if (t < h.t || h.idx == CRT_MAX_U32 || index > h.idx) {
-            h.t = t; h.idx = index; h.ref = CRT_TRI_REF | slot;
-            if (ANYHIT) return;
-          }
-        }
-      }
-      if (sp == 0) return;
-      node = stack[--sp];
-    }
-  }
+  while (trav_step<STATS>(sc.nodes, sc.tri, o, d, idx, idy, idz, exclude, t_min, ANYHIT, h, node, sp, stack, st)) {}
 }
 
-// intersect(), CS:503-518: closest accepted t over all primitives, ties to the highest index.
+// The patches and spheres, in index order with the reference's sequential semantics (CS:508-515).
 template <bool STATS>
-__device__ __forceinline__ Hit intersect(const DevScene& sc, V3 o, V3 d, uint32_t exclude, Stats& st) {
+__device__ __forceinline__ Hit scan_linear(const DevScene& sc, V3 o, V3 d, uint32_t exclude, Stats& st) {
   Hit h; h.t = CRT_INFINITY_F; h.idx = CRT_MAX_U32; h.ref = 0;
   const uint32_t n_c = sc.n_lin < CRT_LIN_PARAM_MAX ? sc.n_lin : CRT_LIN_PARAM_MAX;
   for (uint32_t i = 0; i < n_c; i++) test_lin(sc.lin_c[i], i, o, d, exclude, sc.t_min, h);
   for (uint32_t i = CRT_LIN_PARAM_MAX; i < sc.n_lin; i++) test_lin(sc.lin_g[i], i, o, d, exclude, sc.t_min, h);
   if (STATS) st.prim_tests += sc.n_lin;
+  return h;
+}
+
+// Can the ray reach any triangle at all within [t_min, best]?  Same conservative slab test as a node's.
+__device__ __forceinline__ bool hits_root_box(const DevScene& sc, V3 o, V3 d, float best) {
+  if (sc.n_tri == 0) return false;
+  const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
+  float a0 = (sc.bvh_lo[0] - o.x) * idx, a1 = (sc.bvh_hi[0] - o.x) * idx;
+  float b0 = (sc.bvh_lo[1] - o.y) * idy, b1 = (sc.bvh_hi[1] - o.y) * idy;
+  float c0 = (sc.bvh_lo[2] - o.z) * idz, c1 = (sc.bvh_hi[2] - o.z) * idz;
+  float tn = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), sc.t_min));
+  float tf = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), best));
+  return tn <= tf;
+}
+
+// intersect(), CS:503-518: closest accepted t over all primitives, ties to the highest index.
+template <bool STATS>
+__device__ __forceinline__ Hit intersect(const DevScene& sc, V3 o, V3 d, uint32_t exclude, Stats& st) {
+  Hit h = scan_linear<STATS>(sc, o, d, exclude, st);
   traverse<false, STATS>(sc, o, d, exclude, sc.t_min, h, st);
   return h;
 }
@@ -273,11 +309,7 @@ __device__ __forceinline__ Hit intersect(const DevScene& sc, V3 o, V3 d, uint32_
 // tie rule) settles it: an any-hit traversal bounded by t gives the identical boolean.
 template <bool STATS>
 __device__ __forceinline__ Hit shadow_intersect(const DevScene& sc, V3 o, V3 d, uint32_t include, uint32_t exclude, Stats& st) {
-  Hit h; h.t = CRT_INFINITY_F; h.idx = CRT_MAX_U32; h.ref = 0;
-  const uint32_t n_c = sc.n_lin < CRT_LIN_PARAM_MAX ? sc.n_lin : CRT_LIN_PARAM_MAX;
-  for (uint32_t i = 0; i < n_c; i++) test_lin(sc.lin_c[i], i, o, d, exclude, sc.t_min, h);
-  for (uint32_t i = CRT_LIN_PARAM_MAX; i < sc.n_lin; i++) test_lin(sc.lin_g[i], i, o, d, exclude, sc.t_min, h);
-  if (STATS) st.prim_tests += sc.n_lin;
+  Hit h = scan_linear<STATS>(sc, o, d, exclude, st);
   if (sc.shadow_closest) {
     traverse<false, STATS>(sc, o, d, exclude, sc.t_min, h, st);
   } else if (h.idx == include) {

@@ -29,7 +29,7 @@ LIB_PATH = os.path.join(_HERE, "libcrt.so")
 
 NUM_COUNTERS = 16
 COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits", "tri_tests", "rand",
-                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum", "launches"]
+                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum", "launches", "wf_iterations"]
 SHARD_NONE, SHARD_TILES, SHARD_SPLIT_SPP = 0, 1, 2
 KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
 

@@ -90,7 +90,8 @@ enum crt_counter {
   CRT_CNT_TERM_LIGHT = 9,
   CRT_CNT_TERM_DEPTH = 10,
   CRT_CNT_DEPTH_SUM = 11,   /* sum over paths of depth at termination                     */
-  CRT_CNT_LAUNCHES = 12     /* hot-path kernel launches (counted on the host)             */
+  CRT_CNT_LAUNCHES = 12,    /* hot-path kernel launches (counted on the host)             */
+  CRT_CNT_WF_ITERATIONS = 13 /* wavefront iterations (one ray per live path each)         */
 };
 
 /* requestAdapter/requestDevice + pipeline creation (MJ:8-9, MJ:535-543).  Fails with

@@ -94,11 +94,15 @@ def test_cornell_primary_histogram_matches_survey_pin(gpu, oracle):
     assert int((idx_cpu == 0xFFFFFFFF).sum()) == 25462 or abs(int((idx_cpu == 0xFFFFFFFF).sum()) - 25462) <= 12
 
 
+KERNELS = [pytest.param(1, id="mega"), pytest.param(2, id="wavefront")]
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
 @pytest.mark.parametrize("size,spp,max_depth", [((256, 256), 4, 100), ((320, 180), 3, 100), ((101, 67), 2, 4)])
-def test_cornell_radiance_parity(gpu, oracle, size, spp, max_depth):
+def test_cornell_radiance_parity(gpu, oracle, size, spp, max_depth, kernel):
     ps = scenes.default_scene(*size)
     gpu.set_scene(ps)
-    gpu.set_params(default_params(max_depth=max_depth))
+    gpu.set_params(default_params(max_depth=max_depth, kernel=kernel))
     gpu.reset()
     gpu.frame(spp)
     acc = gpu.accumulator()
@@ -111,11 +115,12 @@ def test_cornell_radiance_parity(gpu, oracle, size, spp, max_depth):
     assert (fb[..., 3] == 255).all()
 
 
-def test_frame_by_frame_equals_batched(gpu, oracle):
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_frame_by_frame_equals_batched(gpu, oracle, kernel):
     """n x dispatch(1) (the reference's frame loop) == dispatch(n) == chunked launches, bit for bit."""
     ps = scenes.default_scene(96, 64)
     gpu.set_scene(ps)
-    gpu.set_params(default_params())
+    gpu.set_params(default_params(kernel=kernel))
     gpu.reset()
     for _ in range(5):
         gpu.frame(1)
@@ -181,10 +186,11 @@ def test_tie_rule_and_coplanar_light(gpu, oracle):
     assert np.array_equal(gt.view(np.uint32), ct.view(np.uint32))
 
 
+@pytest.mark.parametrize("kernel", KERNELS)
 @pytest.mark.parametrize("maker,kw,spp", [(scenes.mesh_scene, dict(n_lon=64, n_lat=32), 3), (scenes.soup_scene, dict(n=4000), 2)])
-def test_triangle_scene_radiance_parity(gpu, oracle, maker, kw, spp):
+def test_triangle_scene_radiance_parity(gpu, oracle, maker, kw, spp, kernel):
     ps = maker(128, 96, **kw)
-    gpu.set_scene(ps); gpu.set_params(default_params(max_depth=8)); gpu.reset(); gpu.reset_counters()
+    gpu.set_scene(ps); gpu.set_params(default_params(max_depth=8, kernel=kernel)); gpu.reset(); gpu.reset_counters()
     gpu.frame(spp)
     acc = gpu.accumulator(); fb = gpu.framebuffer()
     cg = gpu.counters()
@@ -209,10 +215,11 @@ def test_million_triangle_mesh_hits(gpu, oracle):
     assert (gi >= 6).sum() > 5000
 
 
-def test_virtual_ranks_tiles_are_bit_identical(gpu, oracle):
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_virtual_ranks_tiles_are_bit_identical(gpu, oracle, kernel):
     """Tile sharding: the sum of the ranks' accumulators (each zero off its tiles) == the single-GPU result."""
     ps = scenes.default_scene(100, 52)   # ragged edge tiles on both axes
-    gpu.set_scene(ps); gpu.set_params(default_params()); gpu.set_shard(0, 1, 0); gpu.reset()
+    gpu.set_scene(ps); gpu.set_params(default_params(kernel=kernel)); gpu.set_shard(0, 1, 0); gpu.reset()
     gpu.frame(3)
     want = gpu.accumulator()
     total = np.zeros_like(want)
@@ -227,10 +234,11 @@ def test_virtual_ranks_tiles_are_bit_identical(gpu, oracle):
     gpu.set_shard(0, 1, 0)
 
 
-def test_virtual_ranks_split_spp(gpu, oracle):
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_virtual_ranks_split_spp(gpu, oracle, kernel):
     """Split-spp: rank r renders the frames with (sample-1) % world == r; the sum matches within tolerance."""
     ps = scenes.default_scene(80, 60)
-    gpu.set_scene(ps); gpu.set_params(default_params()); gpu.set_shard(0, 1, 0); gpu.reset()
+    gpu.set_scene(ps); gpu.set_params(default_params(kernel=kernel)); gpu.set_shard(0, 1, 0); gpu.reset()
     gpu.frame(6)
     want = gpu.accumulator()
     total = np.zeros_like(want, dtype=np.float32)
@@ -244,6 +252,23 @@ def test_virtual_ranks_split_spp(gpu, oracle):
     gpu.set_shard(0, 1, 0)
     mx, rmse = radiance_errors(total, want, 6)
     assert mx <= MAX_ABS_TOL and rmse <= RMSE_TOL
+
+
+def test_wavefront_detailed_counters_match_oracle(gpu, oracle):
+    """Every device counter of the wavefront path on a triangle scene equals the oracle's (BVH counters aside:
+    the two trees differ, only rays / tests of the linear list / rand calls / termination mix are comparable)."""
+    ps = scenes.mesh_scene(96, 64, n_lon=64, n_lat=32)
+    gpu.set_scene(ps); gpu.set_params(default_params(max_depth=8, kernel=2)); gpu.reset(); gpu.reset_counters()
+    gpu.enable_stats(True)
+    gpu.frame(2)
+    cg = gpu.counters()
+    gpu.enable_stats(False)
+    _, _, cc = oracle.scene(ps, default_params(max_depth=8), use_bvh=True).render(2, want_fb=False)
+    for i, k in enumerate(["paths", "rays_ext", "rays_shadow", "prim_tests", None, None, "rand", "term_miss", "term_rr",
+                           "term_light", "term_depth", "depth_sum"]):
+        if k:
+            assert cg[k] == int(cc[i]), k
+    assert cg["node_visits"] > 0 and cg["tri_tests"] > 0 and cg["wf_iterations"] > 0
 
 
 def test_error_behaviour(gpu):
