@@ -42,15 +42,16 @@ PIXEL_BYTES = 36  # accumulator read 16 + write 16 + framebuffer write 4, once p
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="mesh1m", choices=["mesh1m", "cornell", "soup10m"])
-    ap.add_argument("--spp-per-step", type=int, default=8)
+    ap.add_argument("--spp-per-step", type=int, default=64)
     ap.add_argument("--shard", default="spp", choices=["spp", "tiles"])
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--frames-per-launch", type=int, default=0)
+    ap.add_argument("--pool", type=int, default=0, help="wavefront path slots in flight (0 = library default)")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the secondary Cornell (config 2) measurement")
@@ -249,7 +250,10 @@ def run_b200(args):
     r.set_stream(stream.cuda_stream)
     t0 = time.perf_counter()
     r.set_scene(ps)
-    r.set_params(max_depth=max_depth, frames_per_launch=args.frames_per_launch)
+    p = r.set_params(max_depth=max_depth, frames_per_launch=args.frames_per_launch)
+    if args.pool:
+        p.reserved[1] = args.pool
+        r.set_params(p)
     st = r.scene_stats()   # forces the scene-upload module to run (SoA repack + BVH build)
     r.synchronize()
     setup_s = time.perf_counter() - t0

@@ -64,6 +64,7 @@ struct crt_ctx {
   uint32_t* wf_host_count = nullptr; // pinned: live-slot count read back at check points
   void* wf_stage = nullptr;          // per-sample XYZ staging of the current chunk
   size_t wf_stage_bytes = 0;
+  uint64_t wf_last_work = 0;
   uint32_t wf_last_iters = 0;        // iterations the previous chunk needed (predicts the next check point)
   uint64_t wf_iterations = 0;
 };
@@ -292,12 +293,11 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   // a path needs at most 2*(max_depth+1)+1 rays; keep a chunk's worst case inside the counter arrays
   const uint64_t worst = 2ull * ((uint64_t)ctx->params.max_depth + 2ull);
   if (worst + 2 > CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_ARG, "max_depth %u is too deep for the wavefront kernel; use CRT_KERNEL_MEGA", ctx->params.max_depth);
-  uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 32u;
-  uint32_t lanes_max = ctx->params.reserved[1] ? ctx->params.reserved[1] : 8u;   // reserved[1]: concurrent samples per pixel
+  uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 64u;
+  const uint32_t pool = ctx->params.reserved[1] ? ctx->params.reserved[1] : (8u << 20);   // reserved[1]: path slots in flight
   const size_t n_pixels = ctx->acc_pixels;
-  // memory guards: path state <= ~6 GB, staging <= ~4 GB
-  while (lanes_max > 1 && (uint64_t)n_units * lanes_max * 140ull > (6ull << 30)) lanes_max--;
-  while (chunk > 1 && (uint64_t)n_pixels * chunk * 16ull > (4ull << 30)) chunk--;
+  // guards: staging <= ~8 GB, work items of a chunk < 2^31
+  while (chunk > 1 && ((uint64_t)n_pixels * chunk * 16ull > (8ull << 30) || (uint64_t)n_units * chunk >= (1ull << 31))) chunk--;
   const size_t cnt_bytes = (size_t)(3 * CRT_WF_MAX_ITERS + 4) * 4;
   const bool split = ctx->shard_mode == CRT_SHARD_SPLIT_SPP && ctx->world > 1;
   uint32_t left = n;
@@ -314,12 +314,13 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
     } else {
       ck.s_first = ctx->sample + 1u; ck.s_stride = 1u; ck.n_samples = k;
     }
-    ck.lanes = std::max(1u, std::min(lanes_max, ck.n_samples));
-    const uint64_t iters_worst = worst * ((ck.n_samples + ck.lanes - 1) / ck.lanes) + 2;
-    if (iters_worst > CRT_WF_MAX_ITERS) {   // shrink the chunk so the per-iteration counters cannot run out
-      const uint32_t per_lane = (uint32_t)std::max<uint64_t>(1, (CRT_WF_MAX_ITERS - 2) / worst);
-      chunk = std::max(1u, per_lane * ck.lanes / (split ? ctx->world : 1u));
-      if (chunk < k) continue;
+    const uint64_t total_work = (uint64_t)n_units * ck.n_samples;
+    ck.n_slots = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(total_work, 32), pool);
+    // worst case: every slot runs ceil(total/slots) paths of `worst` rays one after the other
+    const uint64_t iters_worst = worst * ((total_work + ck.n_slots - 1) / ck.n_slots + 1) + 2;
+    if (iters_worst > CRT_WF_MAX_ITERS && k > 1) {   // shrink the chunk so the per-iteration counters cannot run out
+      chunk = std::max(1u, k / 2);
+      continue;
     }
     const size_t stage_bytes = (size_t)std::max(1u, ck.n_samples) * n_pixels * 16;
     if (stage_bytes > ctx->wf_stage_bytes) {
@@ -329,11 +330,11 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
     }
     ck.stage = (float4*)ctx->wf_stage;
     if (ck.n_samples && n_units) {
-      int rc = ensure_wavefront(ctx, n_units * ck.lanes);
+      int rc = ensure_wavefront(ctx, ck.n_slots);
       if (rc) return rc;
       CU(cudaMemsetAsync(ctx->wf.n_active, 0, cnt_bytes, ctx->stream));
       uint32_t it = 0;
-      uint32_t next_check = ctx->wf_last_iters > 4 ? ctx->wf_last_iters - 1 : 2 * ((ck.n_samples + ck.lanes - 1) / ck.lanes) + 1;
+      uint32_t next_check = (ctx->wf_last_iters > 4 && ctx->wf_last_work == total_work) ? ctx->wf_last_iters - 1 : (uint32_t)(2 * (total_work / ck.n_slots) + 2);
       for (;;) {
         CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, grid_l, smem, it, ctx->d_counters, ctx->stream));
         ctx->launches++;
@@ -351,6 +352,7 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
         if (it + 2 >= CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_STATE, "wavefront iteration limit reached");
       }
       ctx->wf_last_iters = it;
+      ctx->wf_last_work = total_work;
       ctx->wf_iterations += it;
     }
     ctx->sample += k;   // UpdateVariables.wgsl:3-8, once per frame

@@ -12,9 +12,10 @@
 //   wf_traverse  persistent warps over the BVH queue; a lane that finishes a ray fetches the next one
 //                (one warp-aggregated atomic per refill), so every trip of the loop has all lanes stepping.
 //
-// Each pixel has C slots ("lanes of the pixel") that render the chunk's samples round-robin, so C samples
-// of every pixel are in flight at once and each iteration's queues are large enough to fill the GPU.  A
-// finished path stores its XYZ in a staging buffer indexed by (sample ordinal, pixel); wf_accumulate then
+// A pool of path slots works through the chunk's (sample, pixel) items: a slot whose path ends takes the next
+// item from a global counter (one atomic per warp), so the queues stay full until the chunk runs out of work
+// and several samples of a pixel are in flight at once.  A finished path stores its XYZ in a staging buffer
+// indexed by (sample ordinal, pixel); wf_accumulate then
 // adds the samples to the accumulator (binding 1) in frame order, as the reference's frames do (CS:108),
 // so results are bit-identical to the megakernel and to n single-frame dispatches.  Queues and counters
 // live in HBM; per-iteration counters are indexed by iteration, so nothing is reset inside the loop.
@@ -28,8 +29,7 @@
 #define WF_FLAG_SHADOW 4u
 #define WF_QUERY_ANYHIT 1u
 
-// unit -> pixel: units enumerate this rank's 8x4 tiles, 32 pixels each (the megakernel's unit order);
-// slot = c * n_units + unit, c = which of the pixel's C concurrent sample lanes
+// unit -> pixel: units enumerate this rank's 8x4 tiles, 32 pixels each (the megakernel's unit order)
 __device__ __forceinline__ bool unit_pixel(const DevScene& sc, uint32_t unit, uint32_t& px, uint32_t& py) {
   uint32_t tile = unit >> 5;
   const uint32_t l = unit & 31u;
@@ -101,84 +101,98 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ Dev
     spectra = s_tables;
     cie = s_tables + ns;
   }
-  const uint32_t n_cur = it == 0 ? ck.n_units * ck.lanes : w.n_active[it];
+  const uint32_t n_cur = it == 0 ? ck.n_slots : w.n_active[it];
   const uint32_t* __restrict__ cur = w.list[it & 1u];
   uint32_t* __restrict__ next = w.list[(it + 1u) & 1u];
+  uint32_t* work = &w.n_active[CRT_WF_MAX_ITERS + 2];   // next unassigned work item of the chunk
+  const uint32_t total_work = ck.n_units * ck.n_samples; // item = ordinal * n_units + unit (sample-major)
+  const uint32_t lane = threadIdx.x & 31u;
 
   Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
   uint32_t n_paths = 0, n_ext = 0, n_shadow = 0, depth_sum = 0;
   uint32_t term_cnt[4] = {0, 0, 0, 0};
 
-  // whole warps iterate together so the queue appends can use warp-wide ballots
+  // whole warps iterate together so the work fetch and the queue appends can use warp-wide ballots
   const uint32_t stride = gridDim.x * blockDim.x;
   const uint32_t n_round = (n_cur + 31u) & ~31u;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
-    bool live = i < n_cur;
-    bool want_bvh = false;
-    uint32_t slot = 0;
-    if (live) {
+    const bool in_range = i < n_cur;
+    bool alive = false, need = false, want_bvh = false;
+    uint32_t slot = 0, wid = 0, px = 0, py = 0;
+    PathState ps;
+    Rng rng;
+    // ---- consume the hit of the slot's current ray
+    if (in_range) {
       slot = it == 0 ? i : cur[i];
-      uint32_t px, py;
-      const uint32_t c = slot / ck.n_units;
-      const bool in_image = unit_pixel(sc, slot - c * ck.n_units, px, py);
-      PathState ps;
-      Rng rng;
-      uint32_t j = c;   // ordinal of the sample this slot works on, within the chunk's owned samples
-      bool alive = false;
-      if (!in_image) {
-        live = false;
-      } else {
-        if (it != 0) {
-          wf_load(w, slot, ps, rng, j);
-          const float4 hv = w.H[slot];
-          Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
-          uint32_t term = 0;
-          alive = path_consume<STATS>(sc, spectra, ps, rng, h, st, &term);
-          if (!alive) {
-            uint32_t lam[4];
-            wavelengths(ps.lam0, lam);
-            const V3 xyz = spectral_to_xyz(cie, ps.L, lam);                    // CS:105
-            const uint32_t pix = px + py * sc.W;                              // CS:107
-            ck.stage[(size_t)j * ck.n_pixels + pix] = make_float4(xyz.x, xyz.y, xyz.z, 0.0f);   // added in order by wf_accumulate
-            if (STATS) { term_cnt[term - TERM_MISS]++; depth_sum += ps.depth; }
-            j += ck.lanes;
-          }
-        }
-        if (!alive && j < ck.n_samples) {
-          path_begin<STATS>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
-          n_paths++;
-          alive = true;
-        }
-        live = alive;
-        if (alive) {
-          // the new ray: linear list here, BVH (if it can matter) in wf_traverse
-          Hit h = scan_linear<STATS>(sc, ps.o, ps.d, ps.exclude, st);
-          uint32_t query = 0;
-          if (!ps.shadow_phase) {
-            n_ext++;
-            want_bvh = hits_root_box(sc, ps.o, ps.d, h.t);
-          } else {
-            n_shadow++;
-            if (sc.shadow_closest) {
-              want_bvh = hits_root_box(sc, ps.o, ps.d, h.t);
-            } else {
-              // only "is the light the closest hit?" matters (crt_device.cuh shadow_intersect)
-              const uint32_t include = __float_as_uint(light_at(sc, ps.light).d1.w);
-              want_bvh = h.idx == include && hits_root_box(sc, ps.o, ps.d, h.t);
-              query = WF_QUERY_ANYHIT;
-            }
-          }
-          wf_store(w, slot, ps, rng, j);
-          w.H[slot] = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), __uint_as_float(query));
+      need = true;
+      if (it != 0) {
+        wf_load(w, slot, ps, rng, wid);
+        const uint32_t j = wid / ck.n_units;
+        unit_pixel(sc, wid - j * ck.n_units, px, py);
+        const float4 hv = w.H[slot];
+        Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
+        uint32_t term = 0;
+        alive = path_consume<STATS>(sc, spectra, ps, rng, h, st, &term);
+        need = !alive;
+        if (!alive) {
+          uint32_t lam[4];
+          wavelengths(ps.lam0, lam);
+          const V3 xyz = spectral_to_xyz(cie, ps.L, lam);                      // CS:105
+          const uint32_t pix = px + py * sc.W;                                // CS:107
+          ck.stage[(size_t)j * ck.n_pixels + pix] = make_float4(xyz.x, xyz.y, xyz.z, 0.0f);   // added in order by wf_accumulate
+          if (STATS) { term_cnt[term - TERM_MISS]++; depth_sum += ps.depth; }
         }
       }
     }
-    wf_push(live, slot, next, &w.n_active[it + 1u]);
+    // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item: one atomic per warp
+    for (;;) {
+      const uint32_t mask = __ballot_sync(0xffffffffu, need);
+      if (mask == 0u) break;
+      uint32_t base = 0;
+      const uint32_t leader = __ffs(mask) - 1u;
+      if (lane == leader) base = atomicAdd(work, (uint32_t)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (need) {
+        wid = base + __popc(mask & ((1u << lane) - 1u));
+        if (wid >= total_work) {
+          need = false;   // the chunk has no work left: this slot retires
+        } else {
+          const uint32_t j = wid / ck.n_units;
+          if (unit_pixel(sc, wid - j * ck.n_units, px, py)) {   // edge tiles have units outside the image
+            path_begin<STATS>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
+            n_paths++;
+            alive = true;
+            need = false;
+          }
+        }
+      }
+    }
+    // ---- the new ray: linear list here, BVH (if it can matter) in wf_traverse
+    if (alive) {
+      Hit h = scan_linear<STATS>(sc, ps.o, ps.d, ps.exclude, st);
+      uint32_t query = 0;
+      if (!ps.shadow_phase) {
+        n_ext++;
+        want_bvh = hits_root_box(sc, ps.o, ps.d, h.t);
+      } else {
+        n_shadow++;
+        if (sc.shadow_closest) {
+          want_bvh = hits_root_box(sc, ps.o, ps.d, h.t);
+        } else {
+          // only "is the light the closest hit?" matters (crt_device.cuh shadow_intersect)
+          const uint32_t include = __float_as_uint(light_at(sc, ps.light).d1.w);
+          want_bvh = h.idx == include && hits_root_box(sc, ps.o, ps.d, h.t);
+          query = WF_QUERY_ANYHIT;
+        }
+      }
+      wf_store(w, slot, ps, rng, wid);
+      w.H[slot] = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), __uint_as_float(query));
+    }
+    wf_push(alive, slot, next, &w.n_active[it + 1u]);
     wf_push(want_bvh, slot, w.bvh_list, &w.n_bvh[it]);
   }
 
   // ---- counters: one atomic per warp and counter
-  const uint32_t lane = threadIdx.x & 31u;
   unsigned long long v[12];
 #pragma unroll
   for (int k = 0; k < 12; k++) v[k] = 0;

@@ -19,7 +19,7 @@ struct WfState {
   float4* H;           // hit of the current ray: t, primitive index, reference, query flags
   uint32_t* list[2];   // live slots of this / the next iteration
   uint32_t* bvh_list;  // slots whose ray must traverse the BVH this iteration
-  uint32_t* n_active;  // [CRT_WF_MAX_ITERS + 1]
+  uint32_t* n_active;  // [CRT_WF_MAX_ITERS + 4]; entry CRT_WF_MAX_ITERS + 2 is the chunk's work counter
   uint32_t* n_bvh;     // [CRT_WF_MAX_ITERS]
   uint32_t* n_fetch;   // [CRT_WF_MAX_ITERS]
   uint32_t tables_in_smem;
@@ -28,7 +28,7 @@ struct WfState {
 // One chunk of frames rendered as a wavefront.
 struct WfChunk {
   uint32_t n_units;     // pixels (8x4-tile order) this rank owns
-  uint32_t lanes;       // C: concurrent sample lanes per pixel; slots = n_units * lanes
+  uint32_t n_slots;     // size of the path-slot pool working on the chunk
   uint32_t n_samples;   // samples of the chunk this rank renders (ordinals 0 .. n_samples-1)
   uint32_t s_first;     // frame number of ordinal 0
   uint32_t s_stride;    // frame number step between ordinals (world size under split-spp, else 1)
