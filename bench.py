@@ -37,6 +37,7 @@ UNIT = "Mrays/s"
 NODE_BYTES = 64   # one BVH2 node fetch (4 x float4), crt_device.cuh traverse()
 TRI_BYTES = 48    # one triangle fetch (3 x float4)
 PIXEL_BYTES = 36  # accumulator read 16 + write 16 + framebuffer write 4, once per pixel per launch
+QUEUE_RAY_BYTES = 84  # wf_traverse per queued ray: queue entry 4 + origin 16 + direction 16 + exclude word 16 + hit read 16 + hit write 16
 
 
 def parse_args():
@@ -155,7 +156,7 @@ def run_reference(args):
         return
     ps, max_depth, desc = workload_scene(args.workload, args.width, args.height)
     threads = os.cpu_count() or 1
-    sw, sh = args.width // 4, args.height // 4
+    sw, sh = args.width // 2, args.height // 2
     sc, _ = oracle_sample(ps, max_depth, sw, sh, 1, threads)
     sample = 0
     for _ in range(args.warmup):
@@ -170,7 +171,7 @@ def run_reference(args):
         rays += int(cnt[1]); shadow += int(cnt[2])
     dt = time.perf_counter() - t0
     value = rays / dt / 1e6
-    sample_desc = f"{sw}x{sh} x 1 frame per step of the same scene (1/16 of the 1080p pixels), {threads} threads"
+    sample_desc = f"{sw}x{sh} x 1 frame per step of the same scene (1/4 of the pixels), {threads} threads"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -206,6 +207,7 @@ def measure(r, stream, torch, dist, args, world, step_frames, flush_buf, device,
     r.reset(); r.reset_counters()
     time_steps(r, stream, torch, args.warmup, step_frames, flush_buf)
     c0 = r.counters()
+    k0 = r.kernel_times()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(device)
@@ -223,8 +225,10 @@ def measure(r, stream, torch, dist, args, world, step_frames, flush_buf, device,
         if world > 1:
             dist.barrier()
     c1 = r.counters()
+    k1 = r.kernel_times()
     d = {k: c1[k] - c0[k] for k in c1}
-    return ms, comb_ms, d, clk.summary()
+    kt = {k: (k1[k][0] - k0[k][0], k1[k][1] - k0[k][1]) for k in k1}
+    return ms, comb_ms, d, clk.summary(), kt
 
 
 def run_b200(args):
@@ -252,7 +256,7 @@ def run_b200(args):
     r.set_scene(ps)
     p = r.set_params(max_depth=max_depth, frames_per_launch=args.frames_per_launch)
     if args.pool:
-        p.reserved[1] = args.pool
+        p.wf_slots = args.pool
         r.set_params(p)
     st = r.scene_stats()   # forces the scene-upload module to run (SoA repack + BVH build)
     r.synchronize()
@@ -276,10 +280,11 @@ def run_b200(args):
     cal = r.counters()
     r.enable_stats(False)
     cal_rays = cal["rays_ext"] + cal["rays_shadow"]
-    bytes_per_ray = (NODE_BYTES * cal["node_visits"] + TRI_BYTES * cal["tri_tests"]) / max(cal_rays, 1)
+    bytes_per_ray = (NODE_BYTES * cal["node_visits"] + TRI_BYTES * cal["tri_tests"] + QUEUE_RAY_BYTES * cal["bvh_rays"]) / max(cal_rays, 1)
 
-    # ---- device-timed region
-    ms, comb_ms, d, clocks = measure(r, stream, torch, dist, args, world, step_frames, flush_buf, device, combine_fn)
+    # ---- device-timed region (events between the hot-path launches give the per-kernel-class times)
+    r.enable_kernel_times(True)
+    ms, comb_ms, d, clocks, kt = measure(r, stream, torch, dist, args, world, step_frames, flush_buf, device, combine_fn)
     total_ms = torch.tensor([sum(ms) + comb_ms], dtype=torch.float64, device=f"cuda:{device}")
     tot = torch.tensor([d["rays_ext"], d["rays_shadow"], d["paths"], d["launches"]], dtype=torch.float64, device=f"cuda:{device}")
     if world > 1:
@@ -289,24 +294,38 @@ def run_b200(args):
     rays_ext, rays_shadow, paths, launches = [float(x) for x in tot.tolist()]
     value = rays_ext / (job_ms * 1e-3) / 1e6
 
-    # ---- roofline of the dominant kernel (pt_megakernel), this rank's launches
+    r.enable_kernel_times(False)
+
+    # ---- roofline of the dominant kernel class, this rank's launches, from the events of the timed region
     peak, peak_src = measured_peaks()
-    my_launches = max(d["launches"], 1)
-    launch_ms = sum(ms) / my_launches
-    pixels_per_launch = args.width * args.height / (world if (world > 1 and args.shard == "tiles") else 1)
-    algo_bytes = bytes_per_ray * (d["rays_ext"] + d["rays_shadow"]) / my_launches + PIXEL_BYTES * pixels_per_launch
+    kt = {k: v for k, v in kt.items() if v[1] > 0}
+    kernel = max(kt, key=lambda k: kt[k][0]) if kt else "pt_megakernel"
+    k_ms, k_n = kt.get(kernel, (sum(ms), max(d["launches"], 1)))
+    launch_ms = k_ms / max(k_n, 1)
+    my_rays = d["rays_ext"] + d["rays_shadow"]
+    pixels_per_step = args.width * args.height / (world if (world > 1 and args.shard == "tiles") else 1)
+    if kernel == "pt_megakernel":
+        total_bytes = bytes_per_ray * my_rays + PIXEL_BYTES * pixels_per_step * k_n
+        what = "64 B x BVH nodes visited + 48 B x triangles tested (device counters) + 36 B x pixels per launch"
+    else:   # wf_traverse (a BVH scene): the traversal kernel's own fetches
+        total_bytes = bytes_per_ray * my_rays
+        what = "64 B x BVH nodes visited + 48 B x triangles tested + 84 B x rays queued (device counters of a calibration step)"
+    algo_bytes = total_bytes / max(k_n, 1)
     achieved = algo_bytes / (launch_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": "pt_megakernel<false>", "launch_ms": launch_ms, "algorithmic_bytes_per_launch": algo_bytes,
+                "kernel": kernel, "launch_ms": launch_ms, "launches": k_n, "share_of_step": k_ms / max(sum(ms), 1e-9),
+                "algorithmic_bytes_per_launch": algo_bytes,
                 "bytes_per_ray": bytes_per_ray, "nodes_per_ray": cal["node_visits"] / max(cal_rays, 1),
-                "tris_per_ray": cal["tri_tests"] / max(cal_rays, 1), "peak_source": peak_src,
-                "note": "algorithmic bytes = 64 B x BVH nodes visited + 48 B x triangles tested (device counters) + 36 B x pixels; "
-                        "fetches served by L1/L2 count, so frac can exceed DRAM traffic / peak (see DESIGN.md)"}
+                "tris_per_ray": cal["tri_tests"] / max(cal_rays, 1), "bvh_rays_per_ray": cal["bvh_rays"] / max(cal_rays, 1),
+                "peak_source": peak_src,
+                "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
+                "note": "algorithmic bytes = " + what + "; fetches served by L1/L2 count, so they exceed DRAM traffic "
+                        "when the scene is L2-resident (see DESIGN.md section 6)"}
     prof = os.path.join(ROOT, "profiles", "r01_traffic.json")
     if os.path.exists(prof):
         try:
             with open(prof) as f:
-                roofline["traffic"] = json.load(f).get(args.workload)
+                roofline["traffic"] = json.load(f).get(args.workload, {}).get(kernel)
         except Exception:
             pass
 
@@ -365,15 +384,19 @@ def run_b200(args):
     if rank == 0 and world == 1:
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            sw, sh = args.width // 4, args.height // 4
+            sw, sh = args.width // 2, args.height // 2
             sc, _ = oracle_sample(ps, max_depth, sw, sh, 1, threads)
-            frames = 2 if args.workload != "cornell" else 4
+            budget_s, frames, ext, shadow, sample = 12.0, 0, 0, 0, 0
             t0 = time.perf_counter()
-            _, _, cnt = sc.render(frames, threads=threads, want_fb=False)
+            while time.perf_counter() - t0 < budget_s:   # whole frames of the same scene until ~12 s of CPU work
+                _, _, cnt = sc.render(1, sample_start=sample, threads=threads, want_fb=False)
+                sample += 1; frames += 1
+                ext += int(cnt[1]); shadow += int(cnt[2])
             dt = time.perf_counter() - t0
-            line["cpu_baseline"] = {"value": int(cnt[1]) / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": f"{sw}x{sh} x {frames} frames of the same scene ({dt:.1f} s of CPU work)",
-                                    "total_mrays_s": (int(cnt[1]) + int(cnt[2])) / dt / 1e6}
+            line["cpu_baseline"] = {"value": ext / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": f"{sw}x{sh} x {frames} frames of the same scene, same max_depth ({dt:.1f} s of CPU work, "
+                                              f"{threads} threads over image rows)",
+                                    "total_mrays_s": (ext + shadow) / dt / 1e6}
         if not args.no_also and args.workload != "cornell":
             from computeraytracer_b200 import scenes
             r.set_scene(scenes.default_scene(args.width, args.height))

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <thread>
 #include <vector>
 
@@ -67,6 +68,12 @@ struct crt_ctx {
   uint64_t wf_last_work = 0;
   uint32_t wf_last_iters = 0;        // iterations the previous chunk needed (predicts the next check point)
   uint64_t wf_iterations = 0;
+
+  // CRT_FLAG_KERNEL_TIMES: events recorded between consecutive hot-path launches
+  std::vector<cudaEvent_t> ev_free;
+  std::vector<std::pair<cudaEvent_t, int>> ev_seq;   // (event, class of the kernel launched right after it; -1 = end of a run)
+  double k_ms[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0};
+  uint64_t k_launches[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0};
 };
 
 namespace {
@@ -87,6 +94,34 @@ int fail(crt_ctx* c, int code, const char* fmt, ...) {
       return fail(ctx, e_ == cudaErrorMemoryAllocation ? CRT_ERR_OOM : CRT_ERR_CUDA, "%s: %s (%s:%d)", #call, \
                   cudaGetErrorString(e_), __FILE__, __LINE__);                                           \
   } while (0)
+
+// CRT_FLAG_KERNEL_TIMES: an event on the stream before the next launch of class `cls` (-1 closes a run)
+cudaError_t mark(crt_ctx* ctx, int cls) {
+  if (!(ctx->params.flags & CRT_FLAG_KERNEL_TIMES)) return cudaSuccess;
+  if (cls < 0 && (ctx->ev_seq.empty() || ctx->ev_seq.back().second < 0)) return cudaSuccess;
+  cudaEvent_t e;
+  if (!ctx->ev_free.empty()) { e = ctx->ev_free.back(); ctx->ev_free.pop_back(); }
+  else { cudaError_t rc = cudaEventCreate(&e); if (rc != cudaSuccess) return rc; }
+  ctx->ev_seq.emplace_back(e, cls);
+  return cudaEventRecord(e, ctx->stream);
+}
+
+// fold the recorded events into k_ms / k_launches; synchronises
+cudaError_t drain_marks(crt_ctx* ctx) {
+  if (ctx->ev_seq.empty()) return cudaSuccess;
+  cudaError_t rc = cudaStreamSynchronize(ctx->stream);
+  if (rc != cudaSuccess) return rc;
+  for (size_t i = 0; i + 1 < ctx->ev_seq.size(); i++) {
+    const int cls = ctx->ev_seq[i].second;
+    if (cls < 0) continue;
+    float ms = 0.0f;
+    if ((rc = cudaEventElapsedTime(&ms, ctx->ev_seq[i].first, ctx->ev_seq[i + 1].first)) != cudaSuccess) return rc;
+    ctx->k_ms[cls] += ms; ctx->k_launches[cls]++;
+  }
+  for (auto& e : ctx->ev_seq) ctx->ev_free.push_back(e.first);
+  ctx->ev_seq.clear();
+  return cudaSuccess;
+}
 
 template <typename T>
 void dfree(T*& p) { if (p) { cudaFree(p); p = nullptr; } }
@@ -294,7 +329,7 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   const uint64_t worst = 2ull * ((uint64_t)ctx->params.max_depth + 2ull);
   if (worst + 2 > CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_ARG, "max_depth %u is too deep for the wavefront kernel; use CRT_KERNEL_MEGA", ctx->params.max_depth);
   uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 64u;
-  const uint32_t pool = ctx->params.reserved[1] ? ctx->params.reserved[1] : (8u << 20);   // reserved[1]: path slots in flight
+  const uint32_t pool = ctx->params.wf_slots ? ctx->params.wf_slots : (8u << 20);
   const size_t n_pixels = ctx->acc_pixels;
   // guards: staging <= ~8 GB, work items of a chunk < 2^31
   while (chunk > 1 && ((uint64_t)n_pixels * chunk * 16ull > (8ull << 30) || (uint64_t)n_units * chunk >= (1ull << 31))) chunk--;
@@ -336,14 +371,17 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       uint32_t it = 0;
       uint32_t next_check = (ctx->wf_last_iters > 4 && ctx->wf_last_work == total_work) ? ctx->wf_last_iters - 1 : (uint32_t)(2 * (total_work / ck.n_slots) + 2);
       for (;;) {
+        CU(mark(ctx, CRT_KC_WF_LOGIC));
         CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, grid_l, smem, it, ctx->d_counters, ctx->stream));
         ctx->launches++;
         if (s.n_tri) {
+          CU(mark(ctx, CRT_KC_WF_TRAVERSE));
           CU(crt::launch_wf_traverse(s, ctx->wf, stats, grid_t, it, ctx->d_counters, ctx->stream));
           ctx->launches++;
         }
         it++;
         if (it >= next_check) {
+          CU(mark(ctx, -1));
           CU(cudaMemcpyAsync(ctx->wf_host_count, ctx->wf.n_active + it, 4, cudaMemcpyDeviceToHost, ctx->stream));
           CU(cudaStreamSynchronize(ctx->stream));
           if (*ctx->wf_host_count == 0) break;
@@ -356,7 +394,9 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       ctx->wf_iterations += it;
     }
     ctx->sample += k;   // UpdateVariables.wgsl:3-8, once per frame
+    CU(mark(ctx, CRT_KC_WF_ACCUMULATE));
     CU(crt::launch_wf_accumulate(s, ck, ctx->d_acc, ctx->d_fb, ctx->sample, ctx->stream));
+    CU(mark(ctx, -1));
     ctx->launches++;
     left -= k;
   }
@@ -427,6 +467,8 @@ void crt_destroy(crt_ctx* ctx) {
   if (ctx->wf_host_count) cudaFreeHost(ctx->wf_host_count);
   if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
   if (ctx->ev_stop) cudaEventDestroy(ctx->ev_stop);
+  for (auto& e : ctx->ev_seq) cudaEventDestroy(e.first);
+  for (auto& e : ctx->ev_free) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -520,7 +562,7 @@ int crt_dispatch_frames(crt_ctx* ctx, uint32_t n) {
   if (rc) return rc;
   if (n > 0xFFFFFFFFu - ctx->sample) return fail(ctx, CRT_ERR_ARG, "frame counter would overflow");
   const DevScene& s = ctx->scene;
-  const bool stats = (ctx->params.reserved[0] & 1u) != 0;   // reserved[0] bit 0: detailed device counters
+  const bool stats = (ctx->params.flags & CRT_FLAG_STATS) != 0;
   uint32_t n_tiles = s.tiles_x * s.tiles_y;
   if (ctx->shard_mode == CRT_SHARD_TILES && ctx->world > 1)
     n_tiles = (n_tiles > ctx->rank) ? (n_tiles - ctx->rank + ctx->world - 1) / ctx->world : 0;
@@ -545,13 +587,16 @@ int crt_dispatch_frames(crt_ctx* ctx, uint32_t n) {
     while (left) {
       const uint32_t k = left < chunk ? left : chunk;
       CU(cudaMemsetAsync(ctx->d_work, 0, 4, ctx->stream));
+      CU(mark(ctx, CRT_KC_MEGA));
       CU(crt::launch_megakernel(s, stats, grid, smem, tables_in_smem, ctx->d_acc, ctx->d_fb, ctx->sample, k, n_units, ctx->d_work,
                                 ctx->d_counters, ctx->stream));
       ctx->sample += k;   // UpdateVariables.wgsl:3-8, once per frame
       ctx->launches++;
       left -= k;
     }
+    CU(mark(ctx, -1));
   }
+  if (ctx->ev_seq.size() > 32768) CU(drain_marks(ctx));
   CU(cudaEventRecord(ctx->ev_stop, ctx->stream));
   ctx->timed = true;
   return CRT_OK;
@@ -668,6 +713,16 @@ int crt_reset_counters(crt_ctx* ctx) {
   CU(cudaMemsetAsync(ctx->d_counters, 0, CRT_NUM_COUNTERS * 8, ctx->stream));
   ctx->launches = 0;
   ctx->wf_iterations = 0;
+  CU(drain_marks(ctx));
+  for (int k = 0; k < CRT_NUM_KERNEL_CLASSES; k++) { ctx->k_ms[k] = 0.0; ctx->k_launches[k] = 0; }
+  return CRT_OK;
+}
+
+int crt_get_kernel_times(crt_ctx* ctx, double* ms, uint64_t* launches, size_t n) {
+  if (!ctx || !ms || !launches) return CRT_ERR_ARG;
+  CU(cudaSetDevice(ctx->device));
+  CU(drain_marks(ctx));
+  for (size_t k = 0; k < n && k < CRT_NUM_KERNEL_CLASSES; k++) { ms[k] = ctx->k_ms[k]; launches[k] = ctx->k_launches[k]; }
   return CRT_OK;
 }
 

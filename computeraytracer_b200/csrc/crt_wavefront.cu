@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ Dev
   const uint32_t lane = threadIdx.x & 31u;
 
   Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
-  uint32_t n_paths = 0, n_ext = 0, n_shadow = 0, depth_sum = 0;
+  uint32_t n_paths = 0, n_ext = 0, n_shadow = 0, depth_sum = 0, n_bvh_rays = 0;
   uint32_t term_cnt[4] = {0, 0, 0, 0};
 
   // whole warps iterate together so the work fetch and the queue appends can use warp-wide ballots
@@ -190,6 +190,7 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ Dev
     }
     wf_push(alive, slot, next, &w.n_active[it + 1u]);
     wf_push(want_bvh, slot, w.bvh_list, &w.n_bvh[it]);
+    n_bvh_rays += want_bvh ? 1u : 0u;
   }
 
   // ---- counters: one atomic per warp and counter
@@ -208,6 +209,11 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ Dev
     unsigned long long x = v[k];
     for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
     if (lane == 0 && x) atomicAdd(&counters[k], x);
+  }
+  {
+    unsigned long long x = n_bvh_rays;
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    if (lane == 0 && x) atomicAdd(&counters[CRT_CNT_BVH_RAYS], x);
   }
 }
 

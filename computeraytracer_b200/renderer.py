@@ -29,9 +29,11 @@ LIB_PATH = os.path.join(_HERE, "libcrt.so")
 
 NUM_COUNTERS = 16
 COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits", "tri_tests", "rand",
-                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum", "launches", "wf_iterations"]
+                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum", "launches", "wf_iterations", "bvh_rays"]
 SHARD_NONE, SHARD_TILES, SHARD_SPLIT_SPP = 0, 1, 2
 KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
+FLAG_STATS, FLAG_KERNEL_TIMES = 1, 2
+KERNEL_CLASSES = ["wf_logic", "wf_traverse", "wf_accumulate", "pt_megakernel"]
 
 STATUS = {0: "CRT_OK", 1: "CRT_ERR_ARG", 2: "CRT_ERR_BINDING", 3: "CRT_ERR_SIZE", 4: "CRT_ERR_STATE",
           5: "CRT_ERR_CUDA", 6: "CRT_ERR_OOM", 7: "CRT_ERR_NODEVICE"}
@@ -46,7 +48,7 @@ class CrtError(RuntimeError):
 class Params(C.Structure):
     """``struct crt_params`` (include/crt.h)."""
     _fields_ = [("max_depth", C.c_uint32), ("grid_size", C.c_uint32), ("t_min", C.c_float), ("exposure", C.c_float),
-                ("kernel", C.c_uint32), ("frames_per_launch", C.c_uint32), ("reserved", C.c_uint32 * 6)]
+                ("kernel", C.c_uint32), ("frames_per_launch", C.c_uint32), ("flags", C.c_uint32), ("wf_slots", C.c_uint32), ("reserved", C.c_uint32 * 4)]
 
 
 _lib = None
@@ -87,6 +89,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.crt_trace_rays.argtypes = [vp, vp, vp, sz, vp, vp]
     lib.crt_get_counters.argtypes = [vp, vp, sz]
     lib.crt_reset_counters.argtypes = [vp]
+    lib.crt_get_kernel_times.argtypes = [vp, vp, vp, sz]
     lib.crt_scene_stats.argtypes = [vp, vp, sz]
     lib.crt_test_detmath.argtypes = [vp, vp, sz, vp, vp, vp, vp]
     if path == LIB_PATH:
@@ -168,7 +171,13 @@ class Renderer:
     def enable_stats(self, on: bool = True) -> None:
         """Detailed device counters (primitive tests, node visits, rand calls, termination mix)."""
         p = self.get_params()
-        p.reserved[0] = (p.reserved[0] | 1) if on else (p.reserved[0] & ~1)
+        p.flags = (p.flags | FLAG_STATS) if on else (p.flags & ~FLAG_STATS)
+        self._ck(self.lib.crt_set_params(self.h, C.byref(p)))
+
+    def enable_kernel_times(self, on: bool = True) -> None:
+        """CUDA events between the hot-path launches, read with :meth:`kernel_times`."""
+        p = self.get_params()
+        p.flags = (p.flags | FLAG_KERNEL_TIMES) if on else (p.flags & ~FLAG_KERNEL_TIMES)
         self._ck(self.lib.crt_set_params(self.h, C.byref(p)))
 
     def set_shard(self, rank: int, world: int, mode: int) -> None:
@@ -243,6 +252,13 @@ class Renderer:
         out = np.zeros(NUM_COUNTERS, dtype=np.uint64)
         self._ck(self.lib.crt_get_counters(self.h, out.ctypes.data, NUM_COUNTERS))
         return {k: int(out[i]) for i, k in enumerate(COUNTER_NAMES)}
+
+    def kernel_times(self) -> dict:
+        """{kernel class: (summed device ms, launches)} since the last reset_counters()."""
+        ms = np.zeros(len(KERNEL_CLASSES), dtype=np.float64)
+        n = np.zeros(len(KERNEL_CLASSES), dtype=np.uint64)
+        self._ck(self.lib.crt_get_kernel_times(self.h, ms.ctypes.data, n.ctypes.data, len(KERNEL_CLASSES)))
+        return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(KERNEL_CLASSES)}
 
     def reset_counters(self) -> None:
         self._ck(self.lib.crt_reset_counters(self.h))

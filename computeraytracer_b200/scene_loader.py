@@ -188,7 +188,9 @@ def load_scene(scene: dict, cie: dict, extra_triangles: Optional[np.ndarray] = N
     # main.js:255-296: lights = primitives whose type is "light", written with the patch fields
     # (origin/edge1/edge2); a sphere light has none of those in the reference (they would be
     # `undefined`), so only patch lights are meaningful.
-    lights = prims[light_rows].copy()
+    # (copied as raw 80-byte rows so the padding lanes stay zero and the bytes are deterministic)
+    raw = prims.view(np.uint8).reshape(-1, PRIM_DTYPE.itemsize)
+    lights = raw[light_rows].copy().reshape(-1).view(PRIM_DTYPE)
 
     cam = scene["camera"]
     return PackedScene(

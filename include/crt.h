@@ -73,8 +73,22 @@ typedef struct crt_params {
   float    exposure;    /* tone_map argument, CS:112 (2.2)                                */
   uint32_t kernel;      /* enum crt_kernel; AUTO picks from the scene         */
   uint32_t frames_per_launch; /* 0 = library default; samples one lane integrates in-register */
-  uint32_t reserved[6];
+  uint32_t flags;       /* CRT_FLAG_* bits (instrumentation; results never depend on them)     */
+  uint32_t wf_slots;    /* wavefront kernel: path slots in flight (0 = library default)        */
+  uint32_t reserved[4];
 } crt_params;
+
+#define CRT_FLAG_STATS 1u        /* detailed device counters (separate, slower kernel variants)   */
+#define CRT_FLAG_KERNEL_TIMES 2u /* CUDA events between hot-path launches: crt_get_kernel_times   */
+
+/* Kernel classes of crt_get_kernel_times. */
+enum crt_kernel_class {
+  CRT_KC_WF_LOGIC = 0,      /* wf_logic: shade / NEE / bounce / regenerate + linear list     */
+  CRT_KC_WF_TRAVERSE = 1,   /* wf_traverse: BVH traversal + triangle tests                   */
+  CRT_KC_WF_ACCUMULATE = 2, /* wf_accumulate: ordered sample sum + epilogue                  */
+  CRT_KC_MEGA = 3,          /* pt_megakernel                                                 */
+  CRT_NUM_KERNEL_CLASSES = 4
+};
 
 #define CRT_NUM_COUNTERS 16
 enum crt_counter {
@@ -91,7 +105,9 @@ enum crt_counter {
   CRT_CNT_TERM_DEPTH = 10,
   CRT_CNT_DEPTH_SUM = 11,   /* sum over paths of depth at termination                     */
   CRT_CNT_LAUNCHES = 12,    /* hot-path kernel launches (counted on the host)             */
-  CRT_CNT_WF_ITERATIONS = 13 /* wavefront iterations (one ray per live path each)         */
+  CRT_CNT_WF_ITERATIONS = 13, /* wavefront iterations (one ray per live path each)        */
+  CRT_CNT_BVH_RAYS = 14     /* wavefront: rays queued for BVH traversal (the rest are settled
+                               by the linear list and the root-box test)                  */
 };
 
 /* requestAdapter/requestDevice + pipeline creation (MJ:8-9, MJ:535-543).  Fails with
@@ -152,6 +168,11 @@ CRT_API int crt_trace_rays(crt_ctx* ctx, const float* rays, const uint32_t* excl
 /* Device-side counters accumulated since the last crt_reset_counters (enum crt_counter). */
 CRT_API int crt_get_counters(crt_ctx* ctx, uint64_t* out, size_t n);
 CRT_API int crt_reset_counters(crt_ctx* ctx);
+
+/* Device time per kernel class (enum crt_kernel_class) since the last crt_reset_counters, measured with
+ * CUDA events recorded on the context's stream between consecutive hot-path launches while
+ * CRT_FLAG_KERNEL_TIMES is set.  ms[k] = summed duration, launches[k] = launches timed.  Synchronises. */
+CRT_API int crt_get_kernel_times(crt_ctx* ctx, double* ms, uint64_t* launches, size_t n);
 
 /* Scene-upload statistics: out[0]=N primitives, [1]=patches+spheres (linear list),
  * [2]=triangles, [3]=BVH nodes, [4]=BVH bytes, [5]=triangle bytes, [6]=build microseconds,

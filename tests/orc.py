@@ -20,7 +20,7 @@ NUM_COUNTERS = 16
 class Params(C.Structure):
     """struct crt_params of include/crt.h"""
     _fields_ = [("max_depth", C.c_uint32), ("grid_size", C.c_uint32), ("t_min", C.c_float), ("exposure", C.c_float),
-                ("kernel", C.c_uint32), ("frames_per_launch", C.c_uint32), ("reserved", C.c_uint32 * 6)]
+                ("kernel", C.c_uint32), ("frames_per_launch", C.c_uint32), ("flags", C.c_uint32), ("wf_slots", C.c_uint32), ("reserved", C.c_uint32 * 4)]
 
 
 def default_params(**kw) -> Params:
