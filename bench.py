@@ -37,6 +37,7 @@ UNIT = "Mrays/s"
 NODE_BYTES = 64   # one BVH2 node fetch (4 x float4), crt_device.cuh traverse()
 TRI_BYTES = 48    # one triangle fetch (3 x float4)
 PIXEL_BYTES = 36  # accumulator read 16 + write 16 + framebuffer write 4, once per pixel per launch
+SHADE_PASS_BYTES = 232  # wf_shade per slot: S0..S5 + H read (112) and written (112), queue entries (8)
 QUEUE_RAY_BYTES = 84  # wf_traverse per queued ray: queue entry 4 + origin 16 + direction 16 + exclude word 16 + hit read 16 + hit write 16
 
 
@@ -307,6 +308,9 @@ def run_b200(args):
     if kernel == "pt_megakernel":
         total_bytes = bytes_per_ray * my_rays + PIXEL_BYTES * pixels_per_step * k_n
         what = "64 B x BVH nodes visited + 48 B x triangles tested (device counters) + 36 B x pixels per launch"
+    elif kernel == "wf_shade":   # path-state traffic: S0..S5 + H read and written once per bounce, queue entries
+        total_bytes = SHADE_PASS_BYTES * (cal["rays_ext"] - cal["term_miss"]) / max(cal_rays, 1) * my_rays
+        what = "232 B of path state (S0..S5, H read + written, queue entries) x surface hits shaded (device counters)"
     else:   # wf_traverse (a BVH scene): the traversal kernel's own fetches
         total_bytes = bytes_per_ray * my_rays
         what = "64 B x BVH nodes visited + 48 B x triangles tested + 84 B x rays queued (device counters of a calibration step)"

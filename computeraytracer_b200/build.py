@@ -34,6 +34,15 @@ def needs_build() -> bool:
     return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
 
 
+def build_variant(out: str, defines: list[str]) -> str:
+    """Tuning aid: the same library with extra -D defines, written to `out` (select it with CRT_LIBCRT=<path>)."""
+    cmd = [nvcc_path(), *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-o", out, *[os.path.join(CSRC, s) for s in SOURCES]]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    return out
+
+
 def build_libcrt(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB

@@ -47,6 +47,7 @@ struct crt_ctx {
   // device state
   float4* d_acc = nullptr;       // binding 1
   uint32_t* d_fb = nullptr;      // binding 0
+  uint32_t* d_tea = nullptr;     // per-pixel tea(x, y*100) of the RNG seed (CS:98)
   size_t acc_pixels = 0;
   float* d_spectra = nullptr; float* d_cie = nullptr;
   void* d_prims_raw = nullptr;   // binding 8 as uploaded
@@ -72,8 +73,8 @@ struct crt_ctx {
   // CRT_FLAG_KERNEL_TIMES: events recorded between consecutive hot-path launches
   std::vector<cudaEvent_t> ev_free;
   std::vector<std::pair<cudaEvent_t, int>> ev_seq;   // (event, class of the kernel launched right after it; -1 = end of a run)
-  double k_ms[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0};
-  uint64_t k_launches[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0};
+  double k_ms[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0, 0};
+  uint64_t k_launches[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0, 0};
 };
 
 namespace {
@@ -129,11 +130,12 @@ void dfree(T*& p) { if (p) { cudaFree(p); p = nullptr; } }
 int ensure_frame_buffers(crt_ctx* ctx) {
   const size_t n = (size_t)ctx->W * ctx->H;
   if (n == ctx->acc_pixels && ctx->d_acc) return CRT_OK;
-  dfree(ctx->d_acc); dfree(ctx->d_fb);
+  dfree(ctx->d_acc); dfree(ctx->d_fb); dfree(ctx->d_tea);
   ctx->acc_pixels = 0;
   if (n == 0) return fail(ctx, CRT_ERR_SIZE, "camera viewport is %ux%u", ctx->W, ctx->H);
   CU(cudaMalloc(&ctx->d_acc, n * sizeof(float4)));
   CU(cudaMalloc(&ctx->d_fb, n * sizeof(uint32_t)));
+  CU(cudaMalloc(&ctx->d_tea, n * sizeof(uint32_t)));
   CU(cudaMemsetAsync(ctx->d_acc, 0, n * sizeof(float4), ctx->stream));   // WebGPU zero-initialises, MJ:298-302
   CU(cudaMemsetAsync(ctx->d_fb, 0, n * sizeof(uint32_t), ctx->stream));
   ctx->acc_pixels = n;
@@ -169,6 +171,8 @@ int upload_camera(crt_ctx* ctx) {
   memcpy(s.eye, out, 12); memcpy(s.hor, out + 3, 12); memcpy(s.ver, out + 6, 12); memcpy(s.llc, out + 9, 12);
   s.W = W; s.H = H;
   s.tiles_x = (W + 7) / 8; s.tiles_y = (H + 3) / 4;
+  CU(crt::launch_tea_tab(W, H, ctx->d_tea, ctx->stream));   // the table is indexed x + y * W, so every camera change rebuilds it
+  s.tea_tab = ctx->d_tea;
   ctx->camera_dirty = false;
   return CRT_OK;
 }
@@ -286,54 +290,52 @@ int prepare(crt_ctx* ctx) {
   return CRT_OK;
 }
 
+constexpr size_t kWfCounterBytes = (size_t)(CRT_WF_MAX_ITERS + 2) * sizeof(WfIter) + 64;   // iteration records + the work counter
+
 int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
   if (ctx->wf_mem && ctx->wf_slots >= n_slots) return CRT_OK;
   if (ctx->wf_mem) { cudaFree(ctx->wf_mem); ctx->wf_mem = nullptr; }
-  const size_t cnt_bytes = (size_t)(3 * CRT_WF_MAX_ITERS + 4) * 4;
-  const size_t total = (size_t)(8 * 16 + 3 * 4) * n_slots + cnt_bytes + 256;   // S0..S6, H; two live lists and the BVH queue
+  // one record per slot; shade and finish queues of two iterations, the regen queue, the BVH queue (2 entries per slot)
+  const size_t total = (size_t)(CRT_WF_REC_WORDS * 16 + 7 * 4) * n_slots + kWfCounterBytes + 256;
   CU(cudaMalloc(&ctx->wf_mem, total));
   uint8_t* p = (uint8_t*)ctx->wf_mem;
   WfState& w = ctx->wf;
-  w.S0 = (float4*)p; p += 16 * (size_t)n_slots;
-  w.S1 = (float4*)p; p += 16 * (size_t)n_slots;
-  w.S2 = (float4*)p; p += 16 * (size_t)n_slots;
-  w.S3 = (float4*)p; p += 16 * (size_t)n_slots;
-  w.S4 = (uint4*)p; p += 16 * (size_t)n_slots;
-  w.S5 = (uint4*)p; p += 16 * (size_t)n_slots;
-  w.S6 = (float4*)p; p += 16 * (size_t)n_slots;
-  w.H = (float4*)p; p += 16 * (size_t)n_slots;
-  w.list[0] = (uint32_t*)p; p += 4 * (size_t)n_slots;
-  w.list[1] = (uint32_t*)p; p += 4 * (size_t)n_slots;
-  w.bvh_list = (uint32_t*)p; p += 4 * (size_t)n_slots;
-  w.n_active = (uint32_t*)p; p += 4 * (size_t)(CRT_WF_MAX_ITERS + 4);
-  w.n_bvh = (uint32_t*)p; p += 4 * (size_t)CRT_WF_MAX_ITERS;
-  w.n_fetch = (uint32_t*)p;
+  w.rec = (float4*)p; p += (size_t)CRT_WF_REC_WORDS * 16 * n_slots;
+  w.bounce[0] = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.bounce[1] = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.finish[0] = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.finish[1] = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.regen = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.bvh_list = (uint32_t*)p; p += 8 * (size_t)n_slots;
+  w.iter = (WfIter*)p; p += (size_t)(CRT_WF_MAX_ITERS + 2) * sizeof(WfIter);
+  w.work = (uint32_t*)p;
   ctx->wf_slots = n_slots;
-  if (!ctx->wf_host_count) CU(cudaMallocHost(&ctx->wf_host_count, 4));
+  if (!ctx->wf_host_count) CU(cudaMallocHost(&ctx->wf_host_count, 8));
   return CRT_OK;
 }
 
-// n frames as a wavefront, in chunks.  Per iteration one wf_logic launch (+ one wf_traverse launch when the
-// scene has triangles); a chunk's loop ends when a check point reads back zero live slots; wf_accumulate then
-// adds the chunk's samples to binding 1 in frame order and rebuilds binding 0.
+// n frames as a wavefront, in chunks.  Iteration 0 starts a path on every slot (wf_regen); every later iteration is
+// wf_shade (one bounce for the slots with a surface hit), wf_regen (finish the slots whose path is over, start new paths on
+// all free slots) and, when the scene has triangles, wf_traverse (the BVH queue both of them filled).  A chunk's loop ends
+// when a check point reads back empty shade and finish queues; wf_accumulate then adds the chunk's samples to binding 1 in
+// frame order and rebuilds binding 0.
 int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   const DevScene& s = ctx->scene;
   size_t smem = crt::wf_tables_bytes(s);
   ctx->wf.tables_in_smem = smem <= 48 * 1024 ? 1u : 0u;
   if (!ctx->wf.tables_in_smem) smem = 0;
-  int bl = 0, bt = 0;
-  CU(crt::wf_config(stats, smem, &bl, &bt));
-  if (bl < 1 || bt < 1) return fail(ctx, CRT_ERR_CUDA, "wavefront kernels do not fit on an SM");
-  const int grid_l = ctx->sm_count * bl, grid_t = ctx->sm_count * bt;
-  // a path needs at most 2*(max_depth+1)+1 rays; keep a chunk's worst case inside the counter arrays
-  const uint64_t worst = 2ull * ((uint64_t)ctx->params.max_depth + 2ull);
+  int bs = 0, br = 0, bt = 0;
+  CU(crt::wf_config(stats, smem, &bs, &br, &bt));
+  if (bs < 1 || br < 1 || bt < 1) return fail(ctx, CRT_ERR_CUDA, "wavefront kernels do not fit on an SM");
+  const int grid_s = ctx->sm_count * bs, grid_r = ctx->sm_count * br, grid_t = ctx->sm_count * bt;
+  // a path lives for at most max_depth+1 extension rays plus one pass for a trailing NEE answer
+  const uint64_t worst = (uint64_t)ctx->params.max_depth + 3ull;
   if (worst + 2 > CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_ARG, "max_depth %u is too deep for the wavefront kernel; use CRT_KERNEL_MEGA", ctx->params.max_depth);
   uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 64u;
   const uint32_t pool = ctx->params.wf_slots ? ctx->params.wf_slots : (8u << 20);
   const size_t n_pixels = ctx->acc_pixels;
   // guards: staging <= ~8 GB, work items of a chunk < 2^31
   while (chunk > 1 && ((uint64_t)n_pixels * chunk * 16ull > (8ull << 30) || (uint64_t)n_units * chunk >= (1ull << 31))) chunk--;
-  const size_t cnt_bytes = (size_t)(3 * CRT_WF_MAX_ITERS + 4) * 4;
   const bool split = ctx->shard_mode == CRT_SHARD_SPLIT_SPP && ctx->world > 1;
   uint32_t left = n;
   while (left) {
@@ -351,7 +353,7 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
     }
     const uint64_t total_work = (uint64_t)n_units * ck.n_samples;
     ck.n_slots = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(total_work, 32), pool);
-    // worst case: every slot runs ceil(total/slots) paths of `worst` rays one after the other
+    // worst case: every slot runs ceil(total/slots) paths of `worst` iterations one after the other
     const uint64_t iters_worst = worst * ((total_work + ck.n_slots - 1) / ck.n_slots + 1) + 2;
     if (iters_worst > CRT_WF_MAX_ITERS && k > 1) {   // shrink the chunk so the per-iteration counters cannot run out
       chunk = std::max(1u, k / 2);
@@ -367,12 +369,17 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
     if (ck.n_samples && n_units) {
       int rc = ensure_wavefront(ctx, ck.n_slots);
       if (rc) return rc;
-      CU(cudaMemsetAsync(ctx->wf.n_active, 0, cnt_bytes, ctx->stream));
+      CU(cudaMemsetAsync(ctx->wf.iter, 0, kWfCounterBytes, ctx->stream));
       uint32_t it = 0;
       uint32_t next_check = (ctx->wf_last_iters > 4 && ctx->wf_last_work == total_work) ? ctx->wf_last_iters - 1 : (uint32_t)(2 * (total_work / ck.n_slots) + 2);
       for (;;) {
-        CU(mark(ctx, CRT_KC_WF_LOGIC));
-        CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, grid_l, smem, it, ctx->d_counters, ctx->stream));
+        if (it) {
+          CU(mark(ctx, CRT_KC_WF_LOGIC));
+          CU(crt::launch_wf_shade(s, ctx->wf, ck, stats, grid_s, smem, it, ctx->d_counters, ctx->stream));
+          ctx->launches++;
+        }
+        CU(mark(ctx, CRT_KC_WF_REGEN));
+        CU(crt::launch_wf_regen(s, ctx->wf, ck, stats, grid_r, smem, it, ctx->d_counters, ctx->stream));
         ctx->launches++;
         if (s.n_tri) {
           CU(mark(ctx, CRT_KC_WF_TRAVERSE));
@@ -382,9 +389,9 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
         it++;
         if (it >= next_check) {
           CU(mark(ctx, -1));
-          CU(cudaMemcpyAsync(ctx->wf_host_count, ctx->wf.n_active + it, 4, cudaMemcpyDeviceToHost, ctx->stream));
+          CU(cudaMemcpyAsync(ctx->wf_host_count, &ctx->wf.iter[it], 8, cudaMemcpyDeviceToHost, ctx->stream));   // n_bounce, n_finish
           CU(cudaStreamSynchronize(ctx->stream));
-          if (*ctx->wf_host_count == 0) break;
+          if (ctx->wf_host_count[0] == 0 && ctx->wf_host_count[1] == 0) break;
           next_check = it + 4;
         }
         if (it + 2 >= CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_STATE, "wavefront iteration limit reached");
@@ -460,7 +467,7 @@ void crt_destroy(crt_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  dfree(ctx->d_acc); dfree(ctx->d_fb); dfree(ctx->d_spectra); dfree(ctx->d_cie); dfree(ctx->d_prims_raw);
+  dfree(ctx->d_acc); dfree(ctx->d_fb); dfree(ctx->d_tea); dfree(ctx->d_spectra); dfree(ctx->d_cie); dfree(ctx->d_prims_raw);
   dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_tri); dfree(ctx->d_nodes); dfree(ctx->d_work); dfree(ctx->d_counters);
   if (ctx->wf_mem) cudaFree(ctx->wf_mem);
   if (ctx->wf_stage) cudaFree(ctx->wf_stage);
@@ -571,6 +578,8 @@ int crt_dispatch_frames(crt_ctx* ctx, uint32_t n) {
   // megakernel for linear-list-only scenes (all lanes share the same primitive loop)
   uint32_t kernel = ctx->params.kernel;
   if (kernel == CRT_KERNEL_AUTO) kernel = (s.n_tri > 0 && ctx->params.max_depth <= 1000) ? CRT_KERNEL_WAVEFRONT : CRT_KERNEL_MEGA;
+  // a light that is itself a triangle needs closest-hit shadow rays: only the megakernel carries that path
+  if (s.shadow_closest) kernel = CRT_KERNEL_MEGA;
   CU(cudaEventRecord(ctx->ev_start, ctx->stream));
   if (kernel == CRT_KERNEL_WAVEFRONT) {
     if (n) { rc = dispatch_wavefront(ctx, n, n_units, stats); if (rc) return rc; }

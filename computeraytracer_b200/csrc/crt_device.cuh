@@ -72,6 +72,7 @@ struct DevScene {
   // sharding
   uint32_t rank, world, shard_mode;
   uint32_t tiles_x, tiles_y;
+  const uint32_t* tea_tab;        // tea(x, y * 100) per pixel (CS:98): depends on the pixel only, hashed once per camera
   LightRec lights_c[CRT_LIGHT_PARAM_MAX];
   LinPrim lin_c[CRT_LIN_PARAM_MAX];
 };

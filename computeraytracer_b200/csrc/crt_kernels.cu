@@ -94,6 +94,13 @@ __global__ void camera_setup_kernel(const float* __restrict__ cam, float vph, fl
   out12[9] = llc.x; out12[10] = llc.y; out12[11] = llc.z;
 }
 
+// seed.w of CS:98, tea(x, y*100): 16 rounds that depend on the pixel only -- hashed once per camera instead of per path
+__global__ void tea_tab_kernel(uint32_t W, uint32_t H, uint32_t* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= W * H) return;
+  out[i] = tea(i % W, (i / W) * 100u);
+}
+
 // ------------------------------------------------------------------------------------------------ the hot path
 // (PathState, path_begin, path_consume, path_step: crt_path.cuh)
 
@@ -264,6 +271,10 @@ cudaError_t launch_repack_tri(const void* prims, const uint32_t* tri_src, uint32
 }
 cudaError_t launch_repack_lights(const void* lights, uint32_t n, LightRec* out, cudaStream_t s) {
   if (n) repack_lights_kernel<<<(n + 127) / 128, 128, 0, s>>>((const RawPrim*)lights, n, out);
+  return cudaGetLastError();
+}
+cudaError_t launch_tea_tab(uint32_t W, uint32_t H, uint32_t* out, cudaStream_t s) {
+  tea_tab_kernel<<<(W * H + 255) / 256, 256, 0, s>>>(W, H, out);
   return cudaGetLastError();
 }
 cudaError_t launch_camera_setup(const float* cam, float vph, float* out12, cudaStream_t s) {

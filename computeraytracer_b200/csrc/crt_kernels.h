@@ -11,6 +11,7 @@ namespace crt {
 cudaError_t launch_repack_lin(const void* prims, const uint32_t* lin_src, uint32_t n, LinPrim* out, cudaStream_t s);
 cudaError_t launch_repack_tri(const void* prims, const uint32_t* tri_src, uint32_t n, float4* out, cudaStream_t s);
 cudaError_t launch_repack_lights(const void* lights, uint32_t n, LightRec* out, cudaStream_t s);
+cudaError_t launch_tea_tab(uint32_t W, uint32_t H, uint32_t* out, cudaStream_t s);
 cudaError_t launch_camera_setup(const float* cam, float vph, float* out12, cudaStream_t s);
 size_t megakernel_tables_bytes(const DevScene& sc);
 cudaError_t megakernel_config(bool stats, size_t smem, int* blocks_per_sm);

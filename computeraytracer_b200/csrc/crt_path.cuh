@@ -144,7 +144,7 @@ __device__ __forceinline__ bool path_consume(const DevScene& sc, const float* __
 // seed + camera_ray + sample_wavelengths + path_trace's initial state, CS:98-101, 121-131
 template <bool STATS>
 __device__ __forceinline__ void path_begin(const DevScene& sc, uint32_t px, uint32_t py, uint32_t sample, PathState& ps, Rng& rng, Stats& st) {
-  rng.x = py; rng.y = px * 100u; rng.z = sample; rng.w = tea(px, py * 100u);   // CS:98
+  rng.x = py; rng.y = px * 100u; rng.z = sample; rng.w = __ldg(&sc.tea_tab[px + py * sc.W]);   // CS:98 (tea_tab_kernel)
   const float G = (float)sc.grid_size;
   const float cell = (float)(sample % sc.grid_size);
   const float s = ((float)px + (cell + rnd(rng)) / G) / (float)sc.W;            // CS:497

@@ -23,11 +23,30 @@
 #include "crt_path.cuh"
 #include "crt_wavefront.h"
 
+#ifndef WF_BLOCK
 #define WF_BLOCK 256
+#endif
+
+// One slot's record: WF_REC_WORDS 16-byte words, contiguous, so that every 32-byte DRAM sector a kernel touches is used
+// in full (the first version kept one array per word: each access pulled a half-used sector from a different DRAM page,
+// and the logic kernels ran at the resulting DRAM traffic, not at their instruction count).  Words that are used together
+// share a sector: wf_traverse reads sectors A and B for an extension ray.
+enum {
+  WF_R_S0 = 0, WF_R_S1 = 1,   // sector A: ray origin + last_bounce_pdf, ray direction + etaScale
+  WF_R_H = 2, WF_R_S5 = 3,    // sector B: hit of the extension ray; exclude, depth|flags|wavelength, sampled light's primitive, work item
+  WF_R_S6 = 4, WF_R_S7 = 5,   // sector C: pending NEE shadow ray (direction, light distance) and contribution
+  WF_R_S2 = 6, WF_R_S3 = 7,   // sector D: accumulated radiance, beta
+  WF_R_S4 = 8                 // sector E: RNG state (+ 16 bytes spare)
+};
+__device__ __forceinline__ float4& wf_f4(const WfState& w, uint32_t slot, int word) { return w.rec[(size_t)slot * WF_REC_WORDS + word]; }
+__device__ __forceinline__ uint4& wf_u4(const WfState& w, uint32_t slot, int word) {
+  return reinterpret_cast<uint4*>(w.rec)[(size_t)slot * WF_REC_WORDS + word];
+}
 #define WF_FLAG_SPECULAR 1u
 #define WF_FLAG_TRANSMISSION 2u
-#define WF_FLAG_SHADOW 4u
-#define WF_QUERY_ANYHIT 1u
+#define WF_FLAG_PENDING 4u            // an NEE contribution (S7) waits for the any-hit answer of its shadow ray (S6)
+#define WF_FLAG_DEAD 8u               // Russian roulette ended the path; only the pending contribution is outstanding
+#define WF_SHADOW_ENTRY 0x80000000u   // BVH queue entry: the slot's shadow ray (otherwise its extension ray)
 
 // unit -> pixel: units enumerate this rank's 8x4 tiles, 32 pixels each (the megakernel's unit order)
 __device__ __forceinline__ bool unit_pixel(const DevScene& sc, uint32_t unit, uint32_t& px, uint32_t& py) {
@@ -39,169 +58,234 @@ __device__ __forceinline__ bool unit_pixel(const DevScene& sc, uint32_t unit, ui
   return px < sc.W && py < sc.H;
 }
 
-__device__ __forceinline__ void wf_load(const WfState& w, uint32_t slot, PathState& ps, Rng& rng, uint32_t& s_cur) {
-  const float4 a = w.S0[slot], b = w.S1[slot];
+__device__ __forceinline__ void wf_load(const WfState& w, uint32_t slot, PathState& ps, Rng& rng, uint32_t& wid, uint32_t& flags) {
+  const float4 a = wf_f4(w, slot, WF_R_S0), b = wf_f4(w, slot, WF_R_S1);
   ps.o = v3(a); ps.pdf = a.w;
   ps.d = v3(b); ps.etaScale = b.w;
-  ps.L = w.S2[slot];
-  ps.beta = w.S3[slot];
-  const uint4 r = w.S4[slot];
+  ps.L = wf_f4(w, slot, WF_R_S2);
+  ps.beta = wf_f4(w, slot, WF_R_S3);
+  const uint4 r = wf_u4(w, slot, WF_R_S4);
   rng.x = r.x; rng.y = r.y; rng.z = r.z; rng.w = r.w;
-  const uint4 m = w.S5[slot];
+  const uint4 m = wf_u4(w, slot, WF_R_S5);
   ps.exclude = m.x;
   ps.depth = m.y & 0xFFFFu;
-  const uint32_t fl = m.y >> 16;
-  ps.specular = (fl & WF_FLAG_SPECULAR) != 0; ps.in_transmission = (fl & WF_FLAG_TRANSMISSION) != 0;
-  ps.shadow_phase = (fl & WF_FLAG_SHADOW) != 0;
-  ps.lam0 = m.z;
-  s_cur = m.w;
-  if (ps.shadow_phase) {
-    const float4 n = w.S6[slot];
-    ps.n = v3(n);
-    const uint32_t rl = __float_as_uint(n.w);
-    ps.refl = rl & 0xFFFu; ps.light = rl >> 12;
-  }
+  flags = (m.y >> 16) & 0xFu;
+  ps.lam0 = m.y >> 20;
+  ps.specular = (flags & WF_FLAG_SPECULAR) != 0; ps.in_transmission = (flags & WF_FLAG_TRANSMISSION) != 0;
+  ps.shadow_phase = false;
+  wid = m.w;
 }
 
-__device__ __forceinline__ void wf_store(const WfState& w, uint32_t slot, const PathState& ps, const Rng& rng, uint32_t s_cur) {
-  w.S0[slot] = make_float4(ps.o.x, ps.o.y, ps.o.z, ps.pdf);
-  w.S1[slot] = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.etaScale);
-  w.S2[slot] = ps.L;
-  w.S3[slot] = ps.beta;
-  w.S4[slot] = make_uint4(rng.x, rng.y, rng.z, rng.w);
-  const uint32_t fl = (ps.specular ? WF_FLAG_SPECULAR : 0u) | (ps.in_transmission ? WF_FLAG_TRANSMISSION : 0u) |
-                      (ps.shadow_phase ? WF_FLAG_SHADOW : 0u);
-  w.S5[slot] = make_uint4(ps.exclude, (ps.depth & 0xFFFFu) | (fl << 16), ps.lam0, s_cur);
-  if (ps.shadow_phase) w.S6[slot] = make_float4(ps.n.x, ps.n.y, ps.n.z, __uint_as_float((ps.refl & 0xFFFu) | (ps.light << 12)));
+__device__ __forceinline__ void wf_store(const WfState& w, uint32_t slot, const PathState& ps, const Rng& rng, uint32_t wid, uint32_t flags,
+                                         uint32_t light_prim) {
+  wf_f4(w, slot, WF_R_S0) = make_float4(ps.o.x, ps.o.y, ps.o.z, ps.pdf);
+  wf_f4(w, slot, WF_R_S1) = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.etaScale);
+  wf_f4(w, slot, WF_R_S2) = ps.L;
+  wf_f4(w, slot, WF_R_S3) = ps.beta;
+  wf_u4(w, slot, WF_R_S4) = make_uint4(rng.x, rng.y, rng.z, rng.w);
+  const uint32_t fl = (flags & (WF_FLAG_PENDING | WF_FLAG_DEAD)) | (ps.specular ? WF_FLAG_SPECULAR : 0u) | (ps.in_transmission ? WF_FLAG_TRANSMISSION : 0u);
+  wf_u4(w, slot, WF_R_S5) = make_uint4(ps.exclude, (ps.depth & 0xFFFFu) | (fl << 16) | (ps.lam0 << 20), light_prim, wid);
 }
 
-// append `slot` to a queue with one atomic per warp
-__device__ __forceinline__ void wf_push(bool pred, uint32_t slot, uint32_t* __restrict__ list, uint32_t* __restrict__ counter) {
-  const uint32_t mask = __ballot_sync(0xffffffffu, pred);   // callers arrive with whole warps
-  if (!pred) return;
-  const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t leader = __ffs(mask) - 1u;
-  uint32_t base = 0;
-  if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
-  base = __shfl_sync(mask, base, leader);
-  list[base + __popc(mask & ((1u << lane) - 1u))] = slot;
+// Appending to a global queue costs one atomic per warp, in two steps so that several queues can be served with the
+// atomics in flight together: wf_reserve issues the atomic (leader lane), wf_commit waits for it and writes the entries.
+// Callers arrive with whole warps.
+struct PushTicket { uint32_t mask, base; };
+
+__device__ __forceinline__ PushTicket wf_reserve(bool pred, uint32_t* __restrict__ counter) {
+  PushTicket t;
+  t.mask = __ballot_sync(0xffffffffu, pred);
+  t.base = 0;
+  if (t.mask != 0u && (threadIdx.x & 31u) == (uint32_t)__ffs(t.mask) - 1u) t.base = atomicAdd(counter, (uint32_t)__popc(t.mask));
+  return t;
 }
 
+__device__ __forceinline__ void wf_commit(const PushTicket& t, bool pred, uint32_t entry, uint32_t* __restrict__ list) {
+  if (t.mask == 0u) return;   // warp-uniform
+  const uint32_t base = __shfl_sync(0xffffffffu, t.base, __ffs(t.mask) - 1);
+  if (pred) list[base + __popc(t.mask & ((1u << (threadIdx.x & 31u)) - 1u))] = entry;
+}
+
+__device__ __forceinline__ void wf_push(bool pred, uint32_t entry, uint32_t* __restrict__ list, uint32_t* __restrict__ counter) {
+  const PushTicket t = wf_reserve(pred, counter);
+  wf_commit(t, pred, entry, list);
+}
+
+// The shadow ray of next-event estimation that still needs the BVH: the light is the closest hit of the linear list at
+// distance t, the contribution c = (BRDF * Le * w / pdf_l) * beta is final unless a triangle occludes the segment.
+struct NeeQuery {
+  bool pending;
+  V3 d;
+  float t;
+  uint32_t light_prim;
+  float4 c;
+};
+
+// One bounce of path_trace's loop body (CS:133-293), entered with the hit `h` of the current extension ray and left with
+// the next extension ray in ps.o / ps.d / ps.exclude.  Unlike path_consume (crt_path.cuh), next-event estimation is not a
+// separate phase: nothing after the shadow ray depends on its outcome except the sum L += BRDF * Le * beta (CS:187) --
+// the light sample, the hemisphere sample, beta and Russian roulette draw the same random numbers either way -- so the
+// bounce is computed in one go and the shadow ray travels with the extension ray.  The linear list answers the shadow
+// query here (CS:697-705: is the closest hit the sampled light?); if it is, and the segment can reach the triangles'
+// bounds, the any-hit BVH query is handed to the caller in `nee` and the contribution is added when its answer arrives,
+// before anything else is added to L, so the order of the float additions is the reference's.
+// Returns 0: the path ended; 1: it continues with an extension ray; 2: Russian roulette ended it while nee.pending
+// (the slot must live on until the contribution has been added).
 template <bool STATS>
-__global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
-                                                     unsigned long long* __restrict__ counters) {
-  extern __shared__ float s_tables[];
-  const float* spectra = sc.spectra;
-  const float* cie = sc.cie;
-  if (w.tables_in_smem) {
-    const uint32_t ns = sc.n_spectra * CRT_LAMBDA_RANGE;
-    for (uint32_t i = threadIdx.x; i < ns; i += blockDim.x) s_tables[i] = sc.spectra[i];
-    for (uint32_t i = threadIdx.x; i < 3u * 471u; i += blockDim.x) s_tables[ns + i] = sc.cie[i];
-    __syncthreads();
-    spectra = s_tables;
-    cie = s_tables + ns;
+__device__ __forceinline__ int wf_bounce(const DevScene& sc, const float* __restrict__ spectra, PathState& ps, Rng& rng, const Hit& h,
+                                         Stats& st, uint32_t* term, uint32_t& n_shadow, NeeQuery& nee) {
+  uint32_t lam[4];
+  wavelengths(ps.lam0, lam);
+  nee.pending = false;
+  if (h.idx == CRT_MAX_U32) { if (STATS) term[0] = TERM_MISS; return 0; }      // CS:141-144
+  ps.exclude = h.idx;                                                         // CS:146
+  const Surface s = surface_of(sc, h, ps.o, ps.d);
+  const uint32_t material = CRT_META_MAT(s.meta);
+  if (material == CRT_MAT_LIGHT) {                                            // CS:149-164
+    const float4 le = sample_spectrum(spectra, sc.n_spectra, CRT_META_EMIS(s.meta), lam);
+    if (ps.depth == 0 || ps.specular) {
+      ps.L.x += ps.beta.x * le.x; ps.L.y += ps.beta.y * le.y; ps.L.z += ps.beta.z * le.z; ps.L.w += ps.beta.w * le.w;
+    } else {
+      const float pdf_l = compute_light_pdf(sc, CRT_META_EMIS(s.meta), s.normal, s.position, ps.o, ps.d);
+      const float w = power_heuristic(ps.pdf, pdf_l);
+      ps.L.x += (w * le.x) * ps.beta.x; ps.L.y += (w * le.y) * ps.beta.y;
+      ps.L.z += (w * le.z) * ps.beta.z; ps.L.w += (w * le.w) * ps.beta.w;
+    }
+    if (STATS) term[0] = TERM_LIGHT;
+    return 0;
   }
-  const uint32_t n_cur = it == 0 ? ck.n_slots : w.n_active[it];
-  const uint32_t* __restrict__ cur = w.list[it & 1u];
-  uint32_t* __restrict__ next = w.list[(it + 1u) & 1u];
-  uint32_t* work = &w.n_active[CRT_WF_MAX_ITERS + 2];   // next unassigned work item of the chunk
-  const uint32_t total_work = ck.n_units * ck.n_samples; // item = ordinal * n_units + unit (sample-major)
+  if (ps.depth >= sc.max_depth) { if (STATS) term[0] = TERM_DEPTH; return 0; }  // CS:167-170
+  if (ps.in_transmission) {                                                   // CS:173-179
+    const float distance = length(ps.o - s.position);
+    const float4 ext = sample_spectrum(spectra, sc.n_spectra, sc.n_spectra - 1, lam);
+    ps.beta.x *= crt_expf(-ext.x * distance); ps.beta.y *= crt_expf(-ext.y * distance);
+    ps.beta.z *= crt_expf(-ext.z * distance); ps.beta.w *= crt_expf(-ext.w * distance);
+  }
+  if (material == CRT_MAT_DIFFUSE) {                                          // CS:182-204
+    // sample_lights + sample_light, CS:341-355
+    const float u0 = rnd(rng);
+    uint32_t li = f2u_sat((float)sc.n_lights * u0);
+    if (li >= sc.n_lights) li = sc.n_lights - 1;
+    const LightRec& light = light_at(sc, li);
+    const float lu = rnd(rng), lv = rnd(rng);
+    const V3 point = madd(madd(v3(light.d1), lu, v3(light.d2)), lv, v3(light.d3));
+    const V3 light_dir = normalize(point - s.position);                       // CS:385
+    // compute_light_radiance, CS:379-408
+    n_shadow++;
+    const uint32_t include = __float_as_uint(light.d1.w);
+    const Hit hs = scan_linear<STATS>(sc, s.position, light_dir, ps.exclude, st);   // shadow_intersect, CS:697-705 (linear list)
+    const float4 refl = sample_spectrum(spectra, sc.n_spectra, CRT_META_REFL(s.meta), lam);
+    const float4 BRDF = make_float4(refl.x / CRT_PI_F, refl.y / CRT_PI_F, refl.z / CRT_PI_F, refl.w / CRT_PI_F);  // CS:184
+    const float cos_theta = fmaxf(0.0f, dot(s.normal, light_dir));             // CS:388
+    const float4 spec = sample_spectrum(spectra, sc.n_spectra, __float_as_uint(light.d2.w), lam);
+    float4 le = make_float4(spec.x * cos_theta, spec.y * cos_theta, spec.z * cos_theta, spec.w * cos_theta);
+    bool add_now = true;
+    if (hs.idx == include) {
+      const Surface sh = surface_of(sc, hs, s.position, light_dir);
+      const float pdf_l = compute_light_pdf(sc, CRT_META_EMIS(sh.meta), sh.normal, sh.position, s.position, light_dir);  // CS:393
+      const float pdf_b = cos_theta / CRT_PI_F;
+      const float w = power_heuristic(pdf_l, pdf_b);
+      le = make_float4(le.x * w / pdf_l, le.y * w / pdf_l, le.z * w / pdf_l, le.w * w / pdf_l);  // CS:400
+      if (hits_root_box(sc, s.position, light_dir, hs.t)) {   // a triangle may still occlude: any-hit query bounded by the light
+        add_now = false;
+        nee.pending = true; nee.d = light_dir; nee.t = hs.t; nee.light_prim = include;
+      }
+    } else {
+      le = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                                // CS:407
+    }
+    const float4 c = make_float4((BRDF.x * le.x) * ps.beta.x, (BRDF.y * le.y) * ps.beta.y, (BRDF.z * le.z) * ps.beta.z,
+                                 (BRDF.w * le.w) * ps.beta.w);                 // CS:187
+    if (add_now) { ps.L.x += c.x; ps.L.y += c.y; ps.L.z += c.z; ps.L.w += c.w; }
+    else nee.c = c;
+    const float u = rnd(rng), v = rnd(rng);
+    if (STATS) st.rand_calls += 5;
+    float pdf;
+    const V3 nd = cosine_hemisphere(s.normal, u, v, pdf);                      // CS:189
+    ps.pdf = pdf;
+    const float cos_b = fabsf(dot(s.normal, nd));                              // CS:190
+    ps.beta.x *= (BRDF.x * cos_b) / pdf; ps.beta.y *= (BRDF.y * cos_b) / pdf;  // CS:192
+    ps.beta.z *= (BRDF.z * cos_b) / pdf; ps.beta.w *= (BRDF.w * cos_b) / pdf;
+    ps.o = s.position; ps.d = nd;
+    ps.specular = false;
+  } else if (material == CRT_MAT_GLASS) {                                     // CS:208-276
+    const float eta1 = 1.0f, eta2 = 1.5f;
+    float eta = eta1 / eta2;
+    const float cos_theta = dot(s.normal, ps.d);
+    const float reflected = fresnel_s(ps.d, s.normal, eta1, eta2);
+    const float pr = reflected, pt = 1.0f - reflected;
+    const float u = rnd(rng);
+    if (STATS) st.rand_calls += 1;
+    V3 current_normal = s.normal;
+    if (cos_theta > 0.0f) { eta = 1.0f / eta; current_normal = -current_normal; }
+    V3 nd;
+    if (u < pr / (pr + pt)) {
+      nd = reflect(ps.d, current_normal);
+    } else {
+      nd = normalize(refract(ps.d, current_normal, eta));
+      const float e2 = eta * eta;
+      ps.beta.x *= e2; ps.beta.y *= e2; ps.beta.z *= e2; ps.beta.w *= e2;
+      ps.etaScale /= e2;
+      ps.in_transmission = !ps.in_transmission;
+    }
+    ps.o = s.position; ps.d = nd;
+    ps.specular = true; ps.exclude = CRT_MAX_U32;
+  }
+  // Russian roulette, CS:279-289
+  const float rx = ps.beta.x * ps.etaScale, ry = ps.beta.y * ps.etaScale, rz = ps.beta.z * ps.etaScale;
+  const float mb = fmaxf(rx, fmaxf(ry, rz));
+  if (ps.depth > 1 && mb < 1.0f) {
+    const float q = fmaxf(0.0f, 1.0f - mb);
+    if (STATS) st.rand_calls += 1;
+    if (rnd(rng) < q) { if (STATS) term[0] = TERM_RR; return nee.pending ? 2 : 0; }
+    const float k = 1.0f - q;
+    ps.beta.x /= k; ps.beta.y /= k; ps.beta.z /= k; ps.beta.w /= k;
+  }
+  ps.depth++;                                                                  // CS:292
+  return 1;
+}
+
+// end of a path: spectral_to_xyz (CS:105) into the staging buffer at (sample ordinal, pixel); wf_accumulate adds in order
+__device__ __forceinline__ void wf_finish(const DevScene& sc, const WfChunk& ck, const float* __restrict__ cie, float4 L, uint32_t lam0, uint32_t wid) {
+  uint32_t lam[4];
+  wavelengths(lam0, lam);
+  const V3 xyz = spectral_to_xyz(cie, L, lam);
+  const uint32_t j = wid / ck.n_units;
+  uint32_t px, py;
+  unit_pixel(sc, wid - j * ck.n_units, px, py);
+  ck.stage[(size_t)j * ck.n_pixels + (px + py * sc.W)] = make_float4(xyz.x, xyz.y, xyz.z, 0.0f);   // CS:107
+}
+
+// the pending NEE contribution of a slot, as the reference would have added it (CS:187 with CS:400 or CS:407)
+__device__ __forceinline__ void wf_add_pending(const WfState& w, uint32_t slot, float4& L) {
+  const bool occluded = wf_f4(w, slot, WF_R_S6).w < 0.0f;   // wf_traverse marks an occluded segment by a negative length
+  float4 c = wf_f4(w, slot, WF_R_S7);
+  if (occluded) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407: Le = 0, the sum still happens
+  L.x += c.x; L.y += c.y; L.z += c.z; L.w += c.w;
+}
+
+struct LogicCounts {
+  uint32_t n_paths, n_ext, n_shadow, depth_sum, n_bvh_rays;
+  uint32_t term_cnt[4];
+};
+
+__device__ __forceinline__ void wf_counts_init(LogicCounts& lc, Stats& st) {
+  st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
+  lc.n_paths = lc.n_ext = lc.n_shadow = lc.depth_sum = lc.n_bvh_rays = 0;
+  lc.term_cnt[0] = lc.term_cnt[1] = lc.term_cnt[2] = lc.term_cnt[3] = 0;
+}
+
+// one atomic per warp and counter
+template <bool STATS>
+__device__ __forceinline__ void wf_counts_flush(const LogicCounts& lc, const Stats& st, unsigned long long* __restrict__ counters) {
   const uint32_t lane = threadIdx.x & 31u;
-
-  Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
-  uint32_t n_paths = 0, n_ext = 0, n_shadow = 0, depth_sum = 0, n_bvh_rays = 0;
-  uint32_t term_cnt[4] = {0, 0, 0, 0};
-
-  // whole warps iterate together so the work fetch and the queue appends can use warp-wide ballots
-  const uint32_t stride = gridDim.x * blockDim.x;
-  const uint32_t n_round = (n_cur + 31u) & ~31u;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
-    const bool in_range = i < n_cur;
-    bool alive = false, need = false, want_bvh = false;
-    uint32_t slot = 0, wid = 0, px = 0, py = 0;
-    PathState ps;
-    Rng rng;
-    // ---- consume the hit of the slot's current ray
-    if (in_range) {
-      slot = it == 0 ? i : cur[i];
-      need = true;
-      if (it != 0) {
-        wf_load(w, slot, ps, rng, wid);
-        const uint32_t j = wid / ck.n_units;
-        unit_pixel(sc, wid - j * ck.n_units, px, py);
-        const float4 hv = w.H[slot];
-        Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
-        uint32_t term = 0;
-        alive = path_consume<STATS>(sc, spectra, ps, rng, h, st, &term);
-        need = !alive;
-        if (!alive) {
-          uint32_t lam[4];
-          wavelengths(ps.lam0, lam);
-          const V3 xyz = spectral_to_xyz(cie, ps.L, lam);                      // CS:105
-          const uint32_t pix = px + py * sc.W;                                // CS:107
-          ck.stage[(size_t)j * ck.n_pixels + pix] = make_float4(xyz.x, xyz.y, xyz.z, 0.0f);   // added in order by wf_accumulate
-          if (STATS) { term_cnt[term - TERM_MISS]++; depth_sum += ps.depth; }
-        }
-      }
-    }
-    // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item: one atomic per warp
-    for (;;) {
-      const uint32_t mask = __ballot_sync(0xffffffffu, need);
-      if (mask == 0u) break;
-      uint32_t base = 0;
-      const uint32_t leader = __ffs(mask) - 1u;
-      if (lane == leader) base = atomicAdd(work, (uint32_t)__popc(mask));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (need) {
-        wid = base + __popc(mask & ((1u << lane) - 1u));
-        if (wid >= total_work) {
-          need = false;   // the chunk has no work left: this slot retires
-        } else {
-          const uint32_t j = wid / ck.n_units;
-          if (unit_pixel(sc, wid - j * ck.n_units, px, py)) {   // edge tiles have units outside the image
-            path_begin<STATS>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
-            n_paths++;
-            alive = true;
-            need = false;
-          }
-        }
-      }
-    }
-    // ---- the new ray: linear list here, BVH (if it can matter) in wf_traverse
-    if (alive) {
-      Hit h = scan_linear<STATS>(sc, ps.o, ps.d, ps.exclude, st);
-      uint32_t query = 0;
-      if (!ps.shadow_phase) {
-        n_ext++;
-        want_bvh = hits_root_box(sc, ps.o, ps.d, h.t);
-      } else {
-        n_shadow++;
-        if (sc.shadow_closest) {
-          want_bvh = hits_root_box(sc, ps.o, ps.d, h.t);
-        } else {
-          // only "is the light the closest hit?" matters (crt_device.cuh shadow_intersect)
-          const uint32_t include = __float_as_uint(light_at(sc, ps.light).d1.w);
-          want_bvh = h.idx == include && hits_root_box(sc, ps.o, ps.d, h.t);
-          query = WF_QUERY_ANYHIT;
-        }
-      }
-      wf_store(w, slot, ps, rng, wid);
-      w.H[slot] = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), __uint_as_float(query));
-    }
-    wf_push(alive, slot, next, &w.n_active[it + 1u]);
-    wf_push(want_bvh, slot, w.bvh_list, &w.n_bvh[it]);
-    n_bvh_rays += want_bvh ? 1u : 0u;
-  }
-
-  // ---- counters: one atomic per warp and counter
   unsigned long long v[12];
 #pragma unroll
   for (int k = 0; k < 12; k++) v[k] = 0;
-  v[CRT_CNT_PATHS] = n_paths; v[CRT_CNT_RAYS_EXT] = n_ext; v[CRT_CNT_RAYS_SHADOW] = n_shadow;
+  v[CRT_CNT_PATHS] = lc.n_paths; v[CRT_CNT_RAYS_EXT] = lc.n_ext; v[CRT_CNT_RAYS_SHADOW] = lc.n_shadow;
   if (STATS) {
     v[CRT_CNT_PRIM_TESTS] = st.prim_tests; v[CRT_CNT_RAND] = st.rand_calls;
-    v[CRT_CNT_TERM_MISS] = term_cnt[0]; v[CRT_CNT_TERM_RR] = term_cnt[1]; v[CRT_CNT_TERM_LIGHT] = term_cnt[2];
-    v[CRT_CNT_TERM_DEPTH] = term_cnt[3]; v[CRT_CNT_DEPTH_SUM] = depth_sum;
+    v[CRT_CNT_TERM_MISS] = lc.term_cnt[0]; v[CRT_CNT_TERM_RR] = lc.term_cnt[1]; v[CRT_CNT_TERM_LIGHT] = lc.term_cnt[2];
+    v[CRT_CNT_TERM_DEPTH] = lc.term_cnt[3]; v[CRT_CNT_DEPTH_SUM] = lc.depth_sum;
   }
 #pragma unroll
   for (int k = 0; k < 12; k++) {
@@ -210,11 +294,212 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ Dev
     for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
     if (lane == 0 && x) atomicAdd(&counters[k], x);
   }
-  {
-    unsigned long long x = n_bvh_rays;
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
-    if (lane == 0 && x) atomicAdd(&counters[CRT_CNT_BVH_RAYS], x);
+  unsigned long long x = lc.n_bvh_rays;
+  for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+  if (lane == 0 && x) atomicAdd(&counters[CRT_CNT_BVH_RAYS], x);
+}
+
+// A live slot leaves a logic kernel.  Its new extension ray meets the linear list here; if it can reach the triangles'
+// bounds it is queued for the BVH (wf_traverse then routes the slot by the final hit), otherwise the hit is final and the
+// slot goes straight to the next iteration's shade queue (surface hit) or finish queue (miss).  A slot that only waits for
+// an NEE answer goes to the finish queue.  Called by whole warps.
+template <bool STATS>
+__device__ __forceinline__ void wf_emit(const DevScene& sc, const WfState& w, uint32_t it, bool alive, bool has_ext, uint32_t slot,
+                                        const PathState& ps, const Rng& rng, uint32_t wid, uint32_t flags, const NeeQuery& nee,
+                                        Stats& st, LogicCounts& lc) {
+  bool want_bvh = false, to_bounce = false;
+  if (has_ext) {
+    const Hit h = scan_linear<STATS>(sc, ps.o, ps.d, ps.exclude, st);
+    lc.n_ext++;
+    want_bvh = hits_root_box(sc, ps.o, ps.d, h.t);
+    to_bounce = !want_bvh && h.idx != CRT_MAX_U32;
+    wf_f4(w, slot, WF_R_H) = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f);
   }
+  const bool to_finish = alive && !want_bvh && !to_bounce;
+  const bool shadow = alive && nee.pending;
+  if (alive) {
+    wf_store(w, slot, ps, rng, wid, flags, nee.light_prim);
+    if (shadow) {
+      wf_f4(w, slot, WF_R_S6) = make_float4(nee.d.x, nee.d.y, nee.d.z, nee.t);
+      wf_f4(w, slot, WF_R_S7) = nee.c;
+    }
+  }
+  const uint32_t nx = (it + 1u) & 1u;
+  // the queue atomics are issued together and waited for together
+  const PushTicket tb = wf_reserve(to_bounce, &w.iter[it + 1u].n_bounce);
+  const PushTicket tf = wf_reserve(to_finish, &w.iter[it + 1u].n_finish);
+  const PushTicket tq = wf_reserve(want_bvh, &w.iter[it].n_bvh);
+  const PushTicket ts = wf_reserve(shadow, &w.iter[it].n_bvh);
+  wf_commit(tb, to_bounce, slot, nx ? w.bounce[1] : w.bounce[0]);
+  wf_commit(tf, to_finish, slot, nx ? w.finish[1] : w.finish[0]);
+  wf_commit(tq, want_bvh, slot, w.bvh_list);
+  wf_commit(ts, shadow, slot | WF_SHADOW_ENTRY, w.bvh_list);
+  lc.n_bvh_rays += (want_bvh ? 1u : 0u) + (shadow ? 1u : 0u);
+}
+
+__device__ __forceinline__ void wf_tables(const DevScene& sc, const WfState& w, float* s_tables, const float*& spectra, const float*& cie) {
+  spectra = sc.spectra;
+  cie = sc.cie;
+  if (w.tables_in_smem) {
+    const uint32_t ns = sc.n_spectra * CRT_LAMBDA_RANGE;
+    for (uint32_t i = threadIdx.x; i < ns; i += blockDim.x) s_tables[i] = sc.spectra[i];
+    for (uint32_t i = threadIdx.x; i < 3u * 471u; i += blockDim.x) s_tables[ns + i] = sc.cie[i];
+    __syncthreads();
+    spectra = s_tables;
+    cie = s_tables + ns;
+  }
+}
+
+// wf_shade: one bounce (wf_bounce) for every slot of the iteration's shade queue -- all lanes of a warp shade.  A path that
+// ends here (light hit, depth limit, Russian roulette with nothing outstanding) is finished and its slot handed to
+// wf_regen through the regen queue.
+#ifndef WF_SHADE_MIN_BLOCKS
+#define WF_SHADE_MIN_BLOCKS 1
+#endif
+#ifndef WF_REGEN_MIN_BLOCKS
+#define WF_REGEN_MIN_BLOCKS 1
+#endif
+#ifndef WF_TRAV_MIN_BLOCKS
+#define WF_TRAV_MIN_BLOCKS 5
+#endif
+template <bool STATS>
+__global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
+                                                     unsigned long long* __restrict__ counters) {
+  extern __shared__ float s_tables[];
+  const float *spectra, *cie;
+  wf_tables(sc, w, s_tables, spectra, cie);
+  const uint32_t n_cur = w.iter[it].n_bounce;
+  const uint32_t* __restrict__ cur = (it & 1u) ? w.bounce[1] : w.bounce[0];
+  Stats st;
+  LogicCounts lc;
+  wf_counts_init(lc, st);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const uint32_t n_round = (n_cur + 31u) & ~31u;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    bool alive = false, has_ext = false, ended = false;
+    uint32_t slot = 0, wid = 0, flags = 0;
+    PathState ps;
+    Rng rng;
+    NeeQuery nee; nee.pending = false; nee.light_prim = 0;
+    if (i < n_cur) {
+      slot = cur[i];
+      wf_load(w, slot, ps, rng, wid, flags);
+      if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // before anything else is added to L
+      const float4 hv = wf_f4(w, slot, WF_R_H);
+      Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
+      uint32_t term = 0;
+      const int r = wf_bounce<STATS>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
+      if (STATS && r != 1) { lc.term_cnt[term - TERM_MISS]++; lc.depth_sum += ps.depth; }
+      flags = (nee.pending ? WF_FLAG_PENDING : 0u) | (r == 2 ? WF_FLAG_DEAD : 0u);
+      alive = r != 0;
+      has_ext = r == 1;
+      ended = r == 0;
+      if (ended) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
+    }
+    const PushTicket tr = wf_reserve(ended, &w.iter[it].n_regen);   // in flight while wf_emit scans the linear list
+    wf_emit<STATS>(sc, w, it, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
+    wf_commit(tr, ended, slot, w.regen);
+  }
+  wf_counts_flush<STATS>(lc, st, counters);
+}
+
+// wf_regen: the free slots of the iteration take the next (sample, pixel) work items (one atomic per warp) and start
+// their paths: seed, camera ray, wavelengths (CS:98-101).  Free slots are: every slot in iteration 0; afterwards the
+// iteration's finish queue (extension ray missed, CS:141-144, or only an NEE answer was outstanding) -- finished here,
+// which is cheap -- followed by the slots wf_shade freed.  A slot retires when the chunk has no work left.
+template <bool STATS>
+__global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
+                                                     unsigned long long* __restrict__ counters) {
+  extern __shared__ float s_tables[];
+  const float *spectra, *cie;
+  wf_tables(sc, w, s_tables, spectra, cie);
+  const uint32_t n_fin = it == 0 ? 0u : w.iter[it].n_finish;
+  const uint32_t n_cur = it == 0 ? ck.n_slots : n_fin + w.iter[it].n_regen;
+  const uint32_t* __restrict__ fin = (it & 1u) ? w.finish[1] : w.finish[0];
+  const uint32_t total_work = ck.n_units * ck.n_samples;   // item = ordinal * n_units + unit (sample-major)
+  const uint32_t lane = threadIdx.x & 31u;
+  Stats st;
+  LogicCounts lc;
+  wf_counts_init(lc, st);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const uint32_t n_round = (n_cur + 31u) & ~31u;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    bool need = i < n_cur, alive = false;
+    uint32_t slot = 0, wid = 0;
+    // the work-item atomic of the first fetch is in flight while the ended paths are finished
+    uint32_t mask = __ballot_sync(0xffffffffu, need);
+    uint32_t first = 0;
+    if (mask != 0u && lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
+    if (need) {
+      if (it == 0) {
+        slot = i;
+      } else if (i < n_fin) {
+        slot = fin[i];
+        const uint4 m = wf_u4(w, slot, WF_R_S5);
+        const uint32_t flags = (m.y >> 16) & 0xFu;
+        float4 L = wf_f4(w, slot, WF_R_S2);
+        if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, L);
+        wf_finish(sc, ck, cie, L, m.y >> 20, m.w);
+        if (STATS && !(flags & WF_FLAG_DEAD)) { lc.term_cnt[0]++; lc.depth_sum += m.y & 0xFFFFu; }
+      } else {
+        slot = w.regen[i - n_fin];
+      }
+    }
+    PathState ps;
+    Rng rng;
+    NeeQuery nee; nee.pending = false; nee.light_prim = 0;
+    while (mask != 0u) {
+      first = __shfl_sync(0xffffffffu, first, __ffs(mask) - 1);
+      if (need) {
+        wid = first + __popc(mask & ((1u << lane) - 1u));
+        if (wid >= total_work) {
+          need = false;   // the chunk has no work left: this slot retires
+        } else {
+          const uint32_t j = wid / ck.n_units;
+          uint32_t px, py;
+          if (unit_pixel(sc, wid - j * ck.n_units, px, py)) {   // edge tiles have units outside the image
+            path_begin<STATS>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
+            lc.n_paths++;
+            alive = true;
+            need = false;
+          }
+        }
+      }
+      mask = __ballot_sync(0xffffffffu, need);   // lanes that drew a unit outside the image fetch again
+      if (mask != 0u && lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
+    }
+    wf_emit<STATS>(sc, w, it, alive, alive, slot, ps, rng, wid, 0u, nee, st, lc);
+  }
+  wf_counts_flush<STATS>(lc, st, counters);
+}
+
+// wf_traverse collects the slots of finished extension rays per warp in shared memory and appends them to the next
+// iteration's queues 32 at a time: one atomic (and one wait for it) per 32 rays instead of one per completion event.
+struct DoneBuf {
+  uint32_t* buf;   // 64 entries of this warp
+  uint32_t n;      // warp-uniform fill
+};
+
+__device__ __forceinline__ void done_flush(DoneBuf& b, uint32_t count, uint32_t* __restrict__ list, uint32_t* __restrict__ counter) {
+  const uint32_t lane = threadIdx.x & 31u;
+  __syncwarp();
+  uint32_t base = 0;
+  if (lane == 0) base = atomicAdd(counter, count);
+  base = __shfl_sync(0xffffffffu, base, 0);
+  if (lane < count) list[base + lane] = b.buf[lane];
+  const uint32_t rest = b.n - count;
+  const uint32_t moved = lane < rest ? b.buf[count + lane] : 0u;
+  __syncwarp();
+  if (lane < rest) b.buf[lane] = moved;
+  b.n = rest;
+}
+
+__device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, uint32_t* __restrict__ list, uint32_t* __restrict__ counter) {
+  const uint32_t mask = __ballot_sync(0xffffffffu, pred);
+  if (mask == 0u) return;
+  if (pred) b.buf[b.n + __popc(mask & ((1u << (threadIdx.x & 31u)) - 1u))] = slot;
+  b.n += __popc(mask);
+  if (b.n >= 32u) done_flush(b, 32u, list, counter);
 }
 
 // Persistent traversal of the BVH queue of iteration `it`.  Each lane owns one ray at a time; when its
@@ -225,13 +510,19 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ Dev
 // trav_inner / trav_leaf (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
 #define WF_INNER_MIN_LANES 12
 template <bool STATS>
-__global__ void __launch_bounds__(WF_BLOCK) wf_traverse(const __grid_constant__ DevScene sc, const WfState w, uint32_t it,
+__global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(const __grid_constant__ DevScene sc, const WfState w, uint32_t it,
                                                         unsigned long long* __restrict__ counters) {
-  const uint32_t n = w.n_bvh[it];
+  __shared__ uint32_t s_done[WF_BLOCK / 32][2][64];
+  const uint32_t n = w.iter[it].n_bvh;
   if (n == 0) return;
+  DoneBuf db_b, db_f;
+  db_b.buf = s_done[threadIdx.x >> 5][0]; db_b.n = 0;
+  db_f.buf = s_done[threadIdx.x >> 5][1]; db_f.n = 0;
+  uint32_t* const list_b = ((it + 1u) & 1u) ? w.bounce[1] : w.bounce[0];
+  uint32_t* const list_f = ((it + 1u) & 1u) ? w.finish[1] : w.finish[0];
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t* __restrict__ queue = w.bvh_list;
-  uint32_t* fetch = &w.n_fetch[it];
+  uint32_t* fetch = &w.iter[it].n_fetch;
   const float4* __restrict__ nodes = sc.nodes;
   const float4* __restrict__ tris = sc.tri;
   const float t_min = sc.t_min;
@@ -240,7 +531,7 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_traverse(const __grid_constant__ 
   int stack[CRT_BVH_STACK];
   int node = 0, sp = 0;
   bool have = false, exhausted = false, anyhit = false;
-  uint32_t slot = 0, exclude = CRT_MAX_U32;
+  uint32_t slot = 0, exclude = CRT_MAX_U32, light_prim = 0;
   V3 o = v3(0.0f, 0.0f, 0.0f), d = v3(0.0f, 0.0f, 1.0f);
   float idx = 0.0f, idy = 0.0f, idz = 0.0f;
   Hit h; h.t = 0.0f; h.idx = CRT_MAX_U32; h.ref = 0;
@@ -259,12 +550,25 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_traverse(const __grid_constant__ 
         if (q >= n) {
           exhausted = true;
         } else {
-          slot = queue[q];
-          const float4 a = w.S0[slot], b = w.S1[slot], hv = w.H[slot];
-          o = v3(a); d = v3(b);
-          exclude = w.S5[slot].x;
-          h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
-          anyhit = (__float_as_uint(hv.w) & WF_QUERY_ANYHIT) != 0u;
+          const uint32_t entry = queue[q];
+          slot = entry & ~WF_SHADOW_ENTRY;
+          anyhit = (entry & WF_SHADOW_ENTRY) != 0u;
+          const float4 a = wf_f4(w, slot, WF_R_S0);
+          const uint4 m = wf_u4(w, slot, WF_R_S5);
+          o = v3(a);
+          exclude = m.x;
+          if (anyhit) {
+            // the NEE shadow ray: the light (linear list) is the closest hit so far at distance b.w; any triangle accepted
+            // under the tie rule within that bound occludes it (crt_device.cuh shadow_intersect)
+            const float4 b = wf_f4(w, slot, WF_R_S6);
+            d = v3(b);
+            light_prim = m.z;
+            h.t = b.w; h.idx = light_prim; h.ref = 0;
+          } else {
+            const float4 b = wf_f4(w, slot, WF_R_S1), hv = wf_f4(w, slot, WF_R_H);
+            d = v3(b);
+            h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
+          }
           idx = 1.0f / d.x; idy = 1.0f / d.y; idz = 1.0f / d.z;
           node = 0; sp = 0;
           have = true;
@@ -291,11 +595,22 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_traverse(const __grid_constant__ 
     if (have && !done && node < 0) {
       if (!trav_leaf<STATS>(tris, o, d, exclude, t_min, anyhit, h, node, sp, stack, st)) done = true;
     }
+    // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
+    //      to the next iteration's shade queue (surface) or finish queue (miss)
+    const bool fin_ext = done && !anyhit;
     if (done) {
-      w.H[slot] = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f);
+      if (anyhit) {
+        if (h.idx != light_prim) reinterpret_cast<float*>(&wf_f4(w, slot, WF_R_S6))[3] = -1.0f;   // occluded
+      } else {
+        wf_f4(w, slot, WF_R_H) = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f);
+      }
       have = false;
     }
+    done_add(db_b, fin_ext && h.idx != CRT_MAX_U32, slot, list_b, &w.iter[it + 1u].n_bounce);
+    done_add(db_f, fin_ext && h.idx == CRT_MAX_U32, slot, list_f, &w.iter[it + 1u].n_finish);
   }
+  if (db_b.n) done_flush(db_b, db_b.n, list_b, &w.iter[it + 1u].n_bounce);
+  if (db_f.n) done_flush(db_f, db_f.n, list_f, &w.iter[it + 1u].n_finish);
   if (STATS) {
     unsigned long long v[2] = {st.node_visits, st.tri_tests};
     for (int k = 0; k < 2; k++) {
@@ -328,22 +643,30 @@ namespace crt {
 
 size_t wf_tables_bytes(const DevScene& sc) { return ((size_t)sc.n_spectra * CRT_LAMBDA_RANGE + 3u * 471u) * sizeof(float); }
 
-cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* trav_blocks_per_sm) {
+cudaError_t wf_config(bool stats, size_t smem, int* shade_blocks_per_sm, int* regen_blocks_per_sm, int* trav_blocks_per_sm) {
   cudaError_t e;
-  if (stats) {
-    if ((e = cudaFuncSetAttribute(wf_logic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<true>, WF_BLOCK, smem)) != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(trav_blocks_per_sm, wf_traverse<true>, WF_BLOCK, 0);
-  }
-  if ((e = cudaFuncSetAttribute(wf_logic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<false>, WF_BLOCK, smem)) != cudaSuccess) return e;
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(trav_blocks_per_sm, wf_traverse<false>, WF_BLOCK, 0);
+#define CRT_WF_CFG(S)                                                                                                              \
+  if ((e = cudaFuncSetAttribute(wf_shade<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaFuncSetAttribute(wf_regen<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(regen_blocks_per_sm, wf_regen<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(trav_blocks_per_sm, wf_traverse<S>, WF_BLOCK, 0);
+  if (stats) { CRT_WF_CFG(true) }
+  CRT_WF_CFG(false)
+#undef CRT_WF_CFG
 }
 
-cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s) {
-  if (stats) wf_logic<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
-  else wf_logic<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  if (stats) wf_shade<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  else wf_shade<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+                            unsigned long long* counters, cudaStream_t s) {
+  if (stats) wf_regen<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  else wf_regen<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
   return cudaGetLastError();
 }
 

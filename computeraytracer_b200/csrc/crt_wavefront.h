@@ -7,21 +7,27 @@ struct DevScene;
 
 #define CRT_WF_MAX_ITERS 8192   // per-iteration counters are indexed by iteration and never reset inside a dispatch
 
-// Path state, one entry per slot (= one owned pixel), structure of arrays of 16-byte words.
+// Queue lengths of one iteration (32 bytes).  Indexed by iteration, so nothing is reset inside a dispatch.
+struct WfIter {
+  uint32_t n_bounce;   // slots whose extension ray hit a surface: wf_shade
+  uint32_t n_finish;   // slots whose path is over (miss, or only an NEE answer was outstanding): wf_regen finishes them
+  uint32_t n_regen;    // slots freed by wf_shade in this iteration: wf_regen starts new paths on them
+  uint32_t n_bvh;      // rays queued for the BVH in this iteration
+  uint32_t n_fetch;    // wf_traverse's fetch cursor into the BVH queue
+  uint32_t pad[3];
+};
+
+#define CRT_WF_REC_WORDS 10     // 16-byte words per slot record (160 bytes = 5 DRAM sectors); layout in crt_wavefront.cu
+#define WF_REC_WORDS CRT_WF_REC_WORDS
+
 struct WfState {
-  float4* S0;          // ray origin, last_bounce_pdf
-  float4* S1;          // ray direction, etaScale
-  float4* S2;          // accumulated radiance (4 wavelengths)
-  float4* S3;          // beta
-  uint4* S4;           // RNG state
-  uint4* S5;           // exclude, depth | flags << 16, first wavelength, current sample ordinal
-  float4* S6;          // shadow phase: surface normal, reflectance | light << 12
-  float4* H;           // hit of the current ray: t, primitive index, reference, query flags
-  uint32_t* list[2];   // live slots of this / the next iteration
-  uint32_t* bvh_list;  // slots whose ray must traverse the BVH this iteration
-  uint32_t* n_active;  // [CRT_WF_MAX_ITERS + 4]; entry CRT_WF_MAX_ITERS + 2 is the chunk's work counter
-  uint32_t* n_bvh;     // [CRT_WF_MAX_ITERS]
-  uint32_t* n_fetch;   // [CRT_WF_MAX_ITERS]
+  float4* rec;         // [slots * WF_REC_WORDS] path state, one contiguous record per slot
+  uint32_t* bounce[2]; // shade queue of this / the next iteration
+  uint32_t* finish[2]; // finish queue of this / the next iteration
+  uint32_t* regen;     // slots freed by wf_shade in the current iteration
+  uint32_t* bvh_list;  // [2 * slots] rays that must traverse the BVH: slot, or slot | 1 << 31 for its shadow ray
+  WfIter* iter;        // [CRT_WF_MAX_ITERS + 2]
+  uint32_t* work;      // next unassigned (sample, pixel) work item of the chunk
   uint32_t tables_in_smem;
 };
 
@@ -38,10 +44,13 @@ struct WfChunk {
 
 namespace crt {
 size_t wf_tables_bytes(const DevScene& sc);
-cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* trav_blocks_per_sm);
-cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+// resident blocks per SM of wf_shade / wf_regen / wf_traverse
+cudaError_t wf_config(bool stats, size_t smem, int* shade_blocks_per_sm, int* regen_blocks_per_sm, int* trav_blocks_per_sm);
+cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
-cudaError_t launch_wf_accumulate(const DevScene& sc, const WfChunk& ck, float4* acc, uint32_t* fb, uint32_t sample_after, cudaStream_t s);
+cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+                            unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, int grid, uint32_t it, unsigned long long* counters,
                                cudaStream_t s);
+cudaError_t launch_wf_accumulate(const DevScene& sc, const WfChunk& ck, float4* acc, uint32_t* fb, uint32_t sample_after, cudaStream_t s);
 }  // namespace crt

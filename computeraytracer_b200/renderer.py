@@ -25,7 +25,7 @@ import numpy as np
 from .scene_loader import PackedScene
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcrt.so")
+LIB_PATH = os.environ.get("CRT_LIBCRT") or os.path.join(_HERE, "libcrt.so")   # CRT_LIBCRT: a tuning build (build.build_variant)
 
 NUM_COUNTERS = 16
 COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits", "tri_tests", "rand",
@@ -33,7 +33,7 @@ COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits"
 SHARD_NONE, SHARD_TILES, SHARD_SPLIT_SPP = 0, 1, 2
 KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
 FLAG_STATS, FLAG_KERNEL_TIMES = 1, 2
-KERNEL_CLASSES = ["wf_logic", "wf_traverse", "wf_accumulate", "pt_megakernel"]
+KERNEL_CLASSES = ["wf_shade", "wf_traverse", "wf_accumulate", "pt_megakernel", "wf_regen"]
 
 STATUS = {0: "CRT_OK", 1: "CRT_ERR_ARG", 2: "CRT_ERR_BINDING", 3: "CRT_ERR_SIZE", 4: "CRT_ERR_STATE",
           5: "CRT_ERR_CUDA", 6: "CRT_ERR_OOM", 7: "CRT_ERR_NODEVICE"}

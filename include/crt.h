@@ -83,11 +83,12 @@ typedef struct crt_params {
 
 /* Kernel classes of crt_get_kernel_times. */
 enum crt_kernel_class {
-  CRT_KC_WF_LOGIC = 0,      /* wf_logic: shade / NEE / bounce / regenerate + linear list     */
+  CRT_KC_WF_LOGIC = 0,      /* wf_shade: one bounce (shade, NEE, Russian roulette) per slot  */
   CRT_KC_WF_TRAVERSE = 1,   /* wf_traverse: BVH traversal + triangle tests                   */
   CRT_KC_WF_ACCUMULATE = 2, /* wf_accumulate: ordered sample sum + epilogue                  */
   CRT_KC_MEGA = 3,          /* pt_megakernel                                                 */
-  CRT_NUM_KERNEL_CLASSES = 4
+  CRT_KC_WF_REGEN = 4,      /* wf_regen: finish ended paths, start new ones on free slots    */
+  CRT_NUM_KERNEL_CLASSES = 5
 };
 
 #define CRT_NUM_COUNTERS 16

@@ -18,9 +18,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def sass_lines(kernel_sub):
     tmp = tempfile.mkdtemp()
-    subprocess.run(["cuobjdump", "-xelf", "all", os.path.join(ROOT, "computeraytracer_b200", "libcrt.so")], cwd=tmp,
+    subprocess.run(["cuobjdump", "-xelf", "all", os.environ.get("CRT_LIB", os.path.join(ROOT, "computeraytracer_b200", "libcrt.so"))], cwd=tmp,
                    check=True, capture_output=True)
-    out = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, "crt_kernels.sm_100a.cubin")], capture_output=True, text=True).stdout
+    out = ""
+    for f in sorted(os.listdir(tmp)):
+        if f.endswith(".cubin"):
+            out += subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
     cur, infn, res = None, False, []
     for ln in out.splitlines():
         if ln.startswith(".text."):
@@ -55,7 +58,8 @@ def main():
     hdr = blk["rows"][0]
     data = blk["rows"][1:]
     ci = {n: i for i, n in enumerate(hdr)}
-    sass = sass_lines(ksub if "Lb" in ksub else "pt_megakernelILb0" if "megakernel" in ksub else ksub)
+    mangled = ksub.replace("<(bool)", "ILb").replace(">", "")
+    sass = sass_lines(mangled if "Lb" in mangled else "pt_megakernelILb0" if "megakernel" in ksub else mangled)
     if len(sass) != len(data):
         print(f"warning: {len(sass)} disassembled instructions vs {len(data)} profiled rows", file=sys.stderr)
     agg = {}
