@@ -54,6 +54,7 @@ def parse_args():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--frames-per-launch", type=int, default=0)
     ap.add_argument("--pool", type=int, default=0, help="wavefront path slots in flight (0 = library default)")
+    ap.add_argument("--wf-split", action="store_true", help="wavefront: wf_shade + wf_regen kernels instead of the single wf_logic")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the secondary Cornell (config 2) measurement")
@@ -256,8 +257,10 @@ def run_b200(args):
     t0 = time.perf_counter()
     r.set_scene(ps)
     p = r.set_params(max_depth=max_depth, frames_per_launch=args.frames_per_launch)
-    if args.pool:
+    if args.pool or args.wf_split:
         p.wf_slots = args.pool
+        if args.wf_split:
+            p.flags |= 4   # CRT_FLAG_WF_SPLIT
         r.set_params(p)
     st = r.scene_stats()   # forces the scene-upload module to run (SoA repack + BVH build)
     r.synchronize()
@@ -308,7 +311,7 @@ def run_b200(args):
     if kernel == "pt_megakernel":
         total_bytes = bytes_per_ray * my_rays + PIXEL_BYTES * pixels_per_step * k_n
         what = "64 B x BVH nodes visited + 48 B x triangles tested (device counters) + 36 B x pixels per launch"
-    elif kernel == "wf_shade":   # path-state traffic: S0..S5 + H read and written once per bounce, queue entries
+    elif kernel in ("wf_shade", "wf_logic"):   # path-state traffic: S0..S5 + H read and written once per bounce, queue entries
         total_bytes = SHADE_PASS_BYTES * (cal["rays_ext"] - cal["term_miss"]) / max(cal_rays, 1) * my_rays
         what = "232 B of path state (S0..S5, H read + written, queue entries) x surface hits shaded (device counters)"
     else:   # wf_traverse (a BVH scene): the traversal kernel's own fetches

@@ -73,8 +73,8 @@ struct crt_ctx {
   // CRT_FLAG_KERNEL_TIMES: events recorded between consecutive hot-path launches
   std::vector<cudaEvent_t> ev_free;
   std::vector<std::pair<cudaEvent_t, int>> ev_seq;   // (event, class of the kernel launched right after it; -1 = end of a run)
-  double k_ms[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0, 0};
-  uint64_t k_launches[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0, 0};
+  double k_ms[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0, 0, 0};
+  uint64_t k_launches[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0, 0, 0};
 };
 
 namespace {
@@ -324,25 +324,26 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   size_t smem = crt::wf_tables_bytes(s);
   ctx->wf.tables_in_smem = smem <= 48 * 1024 ? 1u : 0u;
   if (!ctx->wf.tables_in_smem) smem = 0;
-  int bs = 0, br = 0, bt = 0;
-  CU(crt::wf_config(stats, smem, &bs, &br, &bt));
-  if (bs < 1 || br < 1 || bt < 1) return fail(ctx, CRT_ERR_CUDA, "wavefront kernels do not fit on an SM");
-  const int grid_s = ctx->sm_count * bs, grid_r = ctx->sm_count * br, grid_t = ctx->sm_count * bt;
+  int bl = 0, bs = 0, br = 0, bt = 0;
+  CU(crt::wf_config(stats, smem, &bl, &bs, &br, &bt));
+  if (bl < 1 || bs < 1 || br < 1 || bt < 1) return fail(ctx, CRT_ERR_CUDA, "wavefront kernels do not fit on an SM");
+  const int grid_l = ctx->sm_count * bl, grid_s = ctx->sm_count * bs, grid_r = ctx->sm_count * br, grid_t = ctx->sm_count * bt;
+  const bool split = (ctx->params.flags & CRT_FLAG_WF_SPLIT) != 0;   // three-kernel form (wf_shade / wf_regen) instead of wf_logic
   // a path lives for at most max_depth+1 extension rays plus one pass for a trailing NEE answer
   const uint64_t worst = (uint64_t)ctx->params.max_depth + 3ull;
   if (worst + 2 > CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_ARG, "max_depth %u is too deep for the wavefront kernel; use CRT_KERNEL_MEGA", ctx->params.max_depth);
   uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 64u;
-  const uint32_t pool = ctx->params.wf_slots ? ctx->params.wf_slots : (8u << 20);
+  const uint32_t pool = ctx->params.wf_slots ? ctx->params.wf_slots : (32u << 20);   // measured: 8M -> 114 ms, 16M -> 107 ms, 32M -> 104 ms per 64-spp step of mesh1m
   const size_t n_pixels = ctx->acc_pixels;
   // guards: staging <= ~8 GB, work items of a chunk < 2^31
   while (chunk > 1 && ((uint64_t)n_pixels * chunk * 16ull > (8ull << 30) || (uint64_t)n_units * chunk >= (1ull << 31))) chunk--;
-  const bool split = ctx->shard_mode == CRT_SHARD_SPLIT_SPP && ctx->world > 1;
+  const bool split_spp = ctx->shard_mode == CRT_SHARD_SPLIT_SPP && ctx->world > 1;
   uint32_t left = n;
   while (left) {
     const uint32_t k = left < chunk ? left : chunk;
     WfChunk ck;
     ck.n_units = n_units; ck.n_pixels = (uint32_t)n_pixels;
-    if (split) {
+    if (split_spp) {
       uint32_t first = ctx->sample + 1u;
       first += (ctx->rank + ctx->world - ((first - 1u) % ctx->world)) % ctx->world;
       const uint32_t end = ctx->sample + k;
@@ -373,17 +374,23 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       uint32_t it = 0;
       uint32_t next_check = (ctx->wf_last_iters > 4 && ctx->wf_last_work == total_work) ? ctx->wf_last_iters - 1 : (uint32_t)(2 * (total_work / ck.n_slots) + 2);
       for (;;) {
-        if (it) {
+        if (!split) {
           CU(mark(ctx, CRT_KC_WF_LOGIC));
-          CU(crt::launch_wf_shade(s, ctx->wf, ck, stats, grid_s, smem, it, ctx->d_counters, ctx->stream));
+          CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, grid_l, smem, it, ctx->d_counters, ctx->stream));
+          ctx->launches++;
+        } else {
+          if (it) {
+            CU(mark(ctx, CRT_KC_WF_SHADE));
+            CU(crt::launch_wf_shade(s, ctx->wf, ck, stats, grid_s, smem, it, ctx->d_counters, ctx->stream));
+            ctx->launches++;
+          }
+          CU(mark(ctx, CRT_KC_WF_REGEN));
+          CU(crt::launch_wf_regen(s, ctx->wf, ck, stats, grid_r, smem, it, ctx->d_counters, ctx->stream));
           ctx->launches++;
         }
-        CU(mark(ctx, CRT_KC_WF_REGEN));
-        CU(crt::launch_wf_regen(s, ctx->wf, ck, stats, grid_r, smem, it, ctx->d_counters, ctx->stream));
-        ctx->launches++;
         if (s.n_tri) {
           CU(mark(ctx, CRT_KC_WF_TRAVERSE));
-          CU(crt::launch_wf_traverse(s, ctx->wf, stats, grid_t, it, ctx->d_counters, ctx->stream));
+          CU(crt::launch_wf_traverse(s, ctx->wf, stats, split, grid_t, it, ctx->d_counters, ctx->stream));
           ctx->launches++;
         }
         it++;

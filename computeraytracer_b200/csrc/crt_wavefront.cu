@@ -303,7 +303,7 @@ __device__ __forceinline__ void wf_counts_flush(const LogicCounts& lc, const Sta
 // bounds it is queued for the BVH (wf_traverse then routes the slot by the final hit), otherwise the hit is final and the
 // slot goes straight to the next iteration's shade queue (surface hit) or finish queue (miss).  A slot that only waits for
 // an NEE answer goes to the finish queue.  Called by whole warps.
-template <bool STATS>
+template <bool STATS, bool SPLIT>
 __device__ __forceinline__ void wf_emit(const DevScene& sc, const WfState& w, uint32_t it, bool alive, bool has_ext, uint32_t slot,
                                         const PathState& ps, const Rng& rng, uint32_t wid, uint32_t flags, const NeeQuery& nee,
                                         Stats& st, LogicCounts& lc) {
@@ -315,6 +315,7 @@ __device__ __forceinline__ void wf_emit(const DevScene& sc, const WfState& w, ui
     to_bounce = !want_bvh && h.idx != CRT_MAX_U32;
     wf_f4(w, slot, WF_R_H) = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f);
   }
+  if (!SPLIT) to_bounce = alive;   // single-kernel form: one live list
   const bool to_finish = alive && !want_bvh && !to_bounce;
   const bool shadow = alive && nee.pending;
   if (alive) {
@@ -397,7 +398,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
       if (ended) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
     }
     const PushTicket tr = wf_reserve(ended, &w.iter[it].n_regen);   // in flight while wf_emit scans the linear list
-    wf_emit<STATS>(sc, w, it, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
+    wf_emit<STATS, true>(sc, w, it, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
     wf_commit(tr, ended, slot, w.regen);
   }
   wf_counts_flush<STATS>(lc, st, counters);
@@ -468,7 +469,83 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
       mask = __ballot_sync(0xffffffffu, need);   // lanes that drew a unit outside the image fetch again
       if (mask != 0u && lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
     }
-    wf_emit<STATS>(sc, w, it, alive, alive, slot, ps, rng, wid, 0u, nee, st, lc);
+    wf_emit<STATS, true>(sc, w, it, alive, alive, slot, ps, rng, wid, 0u, nee, st, lc);
+  }
+  wf_counts_flush<STATS>(lc, st, counters);
+}
+
+// wf_logic: the single-kernel form of wf_shade + wf_regen.  One thread per live slot: add the pending NEE answer, shade the
+// hit (wf_bounce), and if the path ended finish it and start the slot's next path right here.  Lanes of a warp are in
+// different phases (ncu: ~14 of 32 active), but these kernels wait on memory and on dependent arithmetic rather than on
+// issue slots, and the fused form makes one pass over a slot's record per bounce instead of up to two.
+template <bool STATS>
+__global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
+                                                     unsigned long long* __restrict__ counters) {
+  extern __shared__ float s_tables[];
+  const float *spectra, *cie;
+  wf_tables(sc, w, s_tables, spectra, cie);
+  const uint32_t n_cur = it == 0 ? ck.n_slots : w.iter[it].n_bounce;
+  const uint32_t* __restrict__ cur = (it & 1u) ? w.bounce[1] : w.bounce[0];
+  const uint32_t total_work = ck.n_units * ck.n_samples;   // item = ordinal * n_units + unit (sample-major)
+  const uint32_t lane = threadIdx.x & 31u;
+  Stats st;
+  LogicCounts lc;
+  wf_counts_init(lc, st);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const uint32_t n_round = (n_cur + 31u) & ~31u;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    bool alive = false, has_ext = false, need = false;
+    uint32_t slot = 0, wid = 0, flags = 0;
+    PathState ps;
+    Rng rng;
+    NeeQuery nee; nee.pending = false; nee.light_prim = 0;
+    if (i < n_cur) {
+      need = true;
+      if (it == 0) {
+        slot = i;
+      } else {
+        slot = cur[i];
+        wf_load(w, slot, ps, rng, wid, flags);
+        if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // before anything else is added to L
+        int r = 0;
+        if (!(flags & WF_FLAG_DEAD)) {
+          const float4 hv = wf_f4(w, slot, WF_R_H);
+          Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
+          uint32_t term = 0;
+          r = wf_bounce<STATS>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
+          if (STATS && r != 1) { lc.term_cnt[term - TERM_MISS]++; lc.depth_sum += ps.depth; }
+        }
+        flags = (nee.pending ? WF_FLAG_PENDING : 0u) | (r == 2 ? WF_FLAG_DEAD : 0u);
+        alive = r != 0;
+        has_ext = r == 1;
+        need = !alive;
+        if (!alive) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
+      }
+    }
+    // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item: one atomic per warp
+    for (;;) {
+      const uint32_t mask = __ballot_sync(0xffffffffu, need);
+      if (mask == 0u) break;
+      uint32_t first = 0;
+      if (lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
+      first = __shfl_sync(0xffffffffu, first, __ffs(mask) - 1);
+      if (need) {
+        wid = first + __popc(mask & ((1u << lane) - 1u));
+        if (wid >= total_work) {
+          need = false;   // the chunk has no work left: this slot retires
+        } else {
+          const uint32_t j = wid / ck.n_units;
+          uint32_t px, py;
+          if (unit_pixel(sc, wid - j * ck.n_units, px, py)) {   // edge tiles have units outside the image
+            path_begin<STATS>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
+            lc.n_paths++;
+            alive = true; has_ext = true; flags = 0; nee.pending = false;
+            need = false;
+          }
+        }
+      }
+    }
+    wf_emit<STATS, false>(sc, w, it, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
   }
   wf_counts_flush<STATS>(lc, st, counters);
 }
@@ -509,7 +586,7 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 // triangle tests do not run at one or two lanes on every trip.  Arithmetic per node and per triangle is
 // trav_inner / trav_leaf (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
 #define WF_INNER_MIN_LANES 12
-template <bool STATS>
+template <bool STATS, bool ROUTE>
 __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(const __grid_constant__ DevScene sc, const WfState w, uint32_t it,
                                                         unsigned long long* __restrict__ counters) {
   __shared__ uint32_t s_done[WF_BLOCK / 32][2][64];
@@ -606,11 +683,15 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
       }
       have = false;
     }
-    done_add(db_b, fin_ext && h.idx != CRT_MAX_U32, slot, list_b, &w.iter[it + 1u].n_bounce);
-    done_add(db_f, fin_ext && h.idx == CRT_MAX_U32, slot, list_f, &w.iter[it + 1u].n_finish);
+    if (ROUTE) {   // three-kernel form: the slot joins the next shade or finish queue by its final hit
+      done_add(db_b, fin_ext && h.idx != CRT_MAX_U32, slot, list_b, &w.iter[it + 1u].n_bounce);
+      done_add(db_f, fin_ext && h.idx == CRT_MAX_U32, slot, list_f, &w.iter[it + 1u].n_finish);
+    }
   }
-  if (db_b.n) done_flush(db_b, db_b.n, list_b, &w.iter[it + 1u].n_bounce);
-  if (db_f.n) done_flush(db_f, db_f.n, list_f, &w.iter[it + 1u].n_finish);
+  if (ROUTE) {
+    if (db_b.n) done_flush(db_b, db_b.n, list_b, &w.iter[it + 1u].n_bounce);
+    if (db_f.n) done_flush(db_f, db_f.n, list_f, &w.iter[it + 1u].n_finish);
+  }
   if (STATS) {
     unsigned long long v[2] = {st.node_visits, st.tri_tests};
     for (int k = 0; k < 2; k++) {
@@ -643,17 +724,27 @@ namespace crt {
 
 size_t wf_tables_bytes(const DevScene& sc) { return ((size_t)sc.n_spectra * CRT_LAMBDA_RANGE + 3u * 471u) * sizeof(float); }
 
-cudaError_t wf_config(bool stats, size_t smem, int* shade_blocks_per_sm, int* regen_blocks_per_sm, int* trav_blocks_per_sm) {
+cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* shade_blocks_per_sm, int* regen_blocks_per_sm,
+                      int* trav_blocks_per_sm) {
   cudaError_t e;
 #define CRT_WF_CFG(S)                                                                                                              \
+  if ((e = cudaFuncSetAttribute(wf_logic<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
   if ((e = cudaFuncSetAttribute(wf_shade<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
   if ((e = cudaFuncSetAttribute(wf_regen<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(regen_blocks_per_sm, wf_regen<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(trav_blocks_per_sm, wf_traverse<S>, WF_BLOCK, 0);
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(trav_blocks_per_sm, wf_traverse<S, true>, WF_BLOCK, 0);
   if (stats) { CRT_WF_CFG(true) }
   CRT_WF_CFG(false)
 #undef CRT_WF_CFG
+}
+
+cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+                            unsigned long long* counters, cudaStream_t s) {
+  if (stats) wf_logic<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  else wf_logic<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
@@ -670,10 +761,15 @@ cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk&
   return cudaGetLastError();
 }
 
-cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, int grid, uint32_t it, unsigned long long* counters,
+cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, int grid, uint32_t it, unsigned long long* counters,
                                cudaStream_t s) {
-  if (stats) wf_traverse<true><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
-  else wf_traverse<false><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
+  if (stats) {
+    if (route) wf_traverse<true, true><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
+    else wf_traverse<true, false><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
+  } else {
+    if (route) wf_traverse<false, true><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
+    else wf_traverse<false, false><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
+  }
   return cudaGetLastError();
 }
 

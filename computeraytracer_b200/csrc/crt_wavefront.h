@@ -44,13 +44,16 @@ struct WfChunk {
 
 namespace crt {
 size_t wf_tables_bytes(const DevScene& sc);
-// resident blocks per SM of wf_shade / wf_regen / wf_traverse
-cudaError_t wf_config(bool stats, size_t smem, int* shade_blocks_per_sm, int* regen_blocks_per_sm, int* trav_blocks_per_sm);
+// resident blocks per SM of wf_logic / wf_shade / wf_regen / wf_traverse
+cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* shade_blocks_per_sm, int* regen_blocks_per_sm,
+                      int* trav_blocks_per_sm);
+cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+                            unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
-cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, int grid, uint32_t it, unsigned long long* counters,
+cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, int grid, uint32_t it, unsigned long long* counters,
                                cudaStream_t s);
 cudaError_t launch_wf_accumulate(const DevScene& sc, const WfChunk& ck, float4* acc, uint32_t* fb, uint32_t sample_after, cudaStream_t s);
 }  // namespace crt

@@ -80,15 +80,18 @@ typedef struct crt_params {
 
 #define CRT_FLAG_STATS 1u        /* detailed device counters (separate, slower kernel variants)   */
 #define CRT_FLAG_KERNEL_TIMES 2u /* CUDA events between hot-path launches: crt_get_kernel_times   */
+#define CRT_FLAG_WF_SPLIT 4u     /* wavefront: wf_shade + wf_regen over compacted queues instead of
+                                    the single wf_logic kernel (same results; tuning/evidence)   */
 
 /* Kernel classes of crt_get_kernel_times. */
 enum crt_kernel_class {
-  CRT_KC_WF_LOGIC = 0,      /* wf_shade: one bounce (shade, NEE, Russian roulette) per slot  */
+  CRT_KC_WF_LOGIC = 0,      /* wf_logic: shade + finish + regenerate, one pass per live slot */
   CRT_KC_WF_TRAVERSE = 1,   /* wf_traverse: BVH traversal + triangle tests                   */
   CRT_KC_WF_ACCUMULATE = 2, /* wf_accumulate: ordered sample sum + epilogue                  */
   CRT_KC_MEGA = 3,          /* pt_megakernel                                                 */
   CRT_KC_WF_REGEN = 4,      /* wf_regen: finish ended paths, start new ones on free slots    */
-  CRT_NUM_KERNEL_CLASSES = 5
+  CRT_KC_WF_SHADE = 5,      /* wf_shade: one bounce per slot of the shade queue (split form) */
+  CRT_NUM_KERNEL_CLASSES = 6
 };
 
 #define CRT_NUM_COUNTERS 16
