@@ -34,7 +34,7 @@ import numpy as np  # noqa: E402
 
 METRIC = "Mrays/s (primary+bounce) at 1080p"
 UNIT = "Mrays/s"
-NODE_BYTES = 64   # one BVH2 node fetch (4 x float4), crt_device.cuh traverse()
+NODE_BYTES = 80   # one 8-wide BVH node fetch (5 x 16 bytes), crt_device.cuh wide_node()
 TRI_BYTES = 48    # one triangle fetch (3 x float4)
 PIXEL_BYTES = 36  # accumulator read 16 + write 16 + framebuffer write 4, once per pixel per launch
 SHADE_PASS_BYTES = 232  # wf_shade per slot: S0..S5 + H read (112) and written (112), queue entries (8)
@@ -310,13 +310,13 @@ def run_b200(args):
     pixels_per_step = args.width * args.height / (world if (world > 1 and args.shard == "tiles") else 1)
     if kernel == "pt_megakernel":
         total_bytes = bytes_per_ray * my_rays + PIXEL_BYTES * pixels_per_step * k_n
-        what = "64 B x BVH nodes visited + 48 B x triangles tested (device counters) + 36 B x pixels per launch"
+        what = "80 B x BVH nodes visited + 48 B x triangles tested (device counters) + 36 B x pixels per launch"
     elif kernel in ("wf_shade", "wf_logic"):   # path-state traffic: S0..S5 + H read and written once per bounce, queue entries
         total_bytes = SHADE_PASS_BYTES * (cal["rays_ext"] - cal["term_miss"]) / max(cal_rays, 1) * my_rays
         what = "232 B of path state (S0..S5, H read + written, queue entries) x surface hits shaded (device counters)"
     else:   # wf_traverse (a BVH scene): the traversal kernel's own fetches
         total_bytes = bytes_per_ray * my_rays
-        what = "64 B x BVH nodes visited + 48 B x triangles tested + 84 B x rays queued (device counters of a calibration step)"
+        what = "80 B x BVH nodes visited + 48 B x triangles tested + 84 B x rays queued (device counters of a calibration step)"
     algo_bytes = total_bytes / max(k_n, 1)
     achieved = algo_bytes / (launch_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,

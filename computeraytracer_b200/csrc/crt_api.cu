@@ -52,7 +52,7 @@ struct crt_ctx {
   float* d_spectra = nullptr; float* d_cie = nullptr;
   void* d_prims_raw = nullptr;   // binding 8 as uploaded
   LinPrim* d_lin = nullptr; LightRec* d_lights = nullptr;
-  float4* d_tri = nullptr; float4* d_nodes = nullptr;
+  float4* d_tri = nullptr; uint4* d_nodes = nullptr;
   uint32_t* d_work = nullptr;
   unsigned long long* d_counters = nullptr;
   DevScene scene;
@@ -269,7 +269,7 @@ int upload_scene(crt_ctx* ctx) {
   }
   const auto t1 = std::chrono::steady_clock::now();
   ctx->stats[0] = n_prims; ctx->stats[1] = s.n_lin; ctx->stats[2] = s.n_tri; ctx->stats[3] = s.n_nodes;
-  ctx->stats[4] = (uint64_t)s.n_nodes * 64; ctx->stats[5] = (uint64_t)s.n_tri * 48;
+  ctx->stats[4] = (uint64_t)s.n_nodes * 80; ctx->stats[5] = (uint64_t)s.n_tri * 48;
   ctx->stats[6] = (uint64_t)std::chrono::duration_cast<std::chrono::microseconds>(t1 - t0).count();
   ctx->stats[7] = bvh.max_depth;
   ctx->scene_dirty = false;

@@ -18,7 +18,7 @@ namespace crt {
 namespace {
 
 constexpr int kBins = 32;
-constexpr uint32_t kLeafMax = 8;         // leaf encoding holds count-1 in 3 bits
+constexpr uint32_t kLeafMax = 3;         // a wide node's meta byte holds the leaf's triangle count in 3 unary bits
 constexpr uint32_t kForceMedianDepth = 36;
 constexpr float kTraversalCost = 1.0f;   // relative to one triangle test
 
@@ -115,7 +115,6 @@ struct Builder {
     }
     if (!have_split) {
       if (count <= kLeafMax && depth < kForceMedianDepth) { n.count = count; return; }
-      if (count <= 4) { n.count = count; return; }
       // object median along the widest centroid axis (also the fallback for coincident centroids)
       int ax = 0;
       float e0 = cbox.hi[0] - cbox.lo[0], e1 = cbox.hi[1] - cbox.lo[1], e2 = cbox.hi[2] - cbox.lo[2];
@@ -141,10 +140,21 @@ struct Builder {
   }
 };
 
-inline int32_t child_code(const std::vector<BNode>& pool, uint32_t c, const std::vector<int32_t>& inner_index) {
-  const BNode& n = pool[c];
-  if (n.count) return ~(int32_t)((n.first << 3) | (n.count - 1));
-  return inner_index[c];
+// ---- collapse to an 8-wide BVH with quantised child boxes (node layout: crt_device.cuh, "Wide8")
+struct WideChild { uint32_t bvh2; float c[3]; };
+
+inline uint32_t f2u(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+
+// exponent e with 2^e >= ext / 255, as the biased byte of a float (so the device builds 2^e with one shift)
+inline uint32_t scale_exp(float ext) {
+  int e = -126;
+  if (ext > 0.0f) {
+    e = (int)std::ceil(std::log2((double)ext / 255.0));
+    while (std::ldexp(255.0, e) < (double)ext) e++;   // guard against log2 rounding
+    if (e < -126) e = -126;
+    if (e > 127) e = 127;
+  }
+  return (uint32_t)(e + 127);
 }
 
 }  // namespace
@@ -175,51 +185,96 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
 
   Builder b(items, n_threads < 1 ? 1 : n_threads);
   b.build(0, 0, (uint32_t)n, 0);
-  out.max_depth = b.max_depth.load();
-
-  out.tri_src.resize(n);
-  for (size_t i = 0; i < n; i++) out.tri_src[i] = items[i].id;
-
-  // flatten: inner nodes in depth-first order (left subtree right after its parent)
   const std::vector<BNode>& pool = b.pool;
-  std::vector<int32_t> inner_index(pool.size(), -1);
-  std::vector<uint32_t> order;
-  if (pool[0].count) {
-    // a lone leaf: wrap it so the root is an inner node; the second child is an empty box
-    out.nodes.assign(16, 0.0f);
-    float* q = out.nodes.data();
-    const BNode& r = pool[0];
-    q[0] = r.box.lo[0] - pad; q[1] = r.box.hi[0] + pad; q[2] = r.box.lo[1] - pad; q[3] = r.box.hi[1] + pad;
-    q[4] = 1e30f; q[5] = -1e30f; q[6] = 1e30f; q[7] = -1e30f;
-    q[8] = r.box.lo[2] - pad; q[9] = r.box.hi[2] + pad; q[10] = 1e30f; q[11] = -1e30f;
-    int32_t c0 = ~(int32_t)((r.first << 3) | (r.count - 1));
-    std::memcpy(&q[12], &c0, 4); std::memcpy(&q[13], &c0, 4);
-    out.n_nodes = 1;
-    return;
+
+  // Wide nodes are created breadth-first: the inner children of a node get consecutive indices (child_base + rank in
+  // slot order), its leaf children's triangles consecutive slots from tri_base (offset + count <= 24).
+  std::vector<uint32_t> wide_src{0};      // wide node -> BVH2 node it was collapsed from
+  std::vector<uint32_t> wide_depth{1};
+  out.tri_src.reserve(n);
+  out.nodes.reserve((n / 2 + 16) * 20);
+  for (size_t k = 0; k < wide_src.size(); k++) {
+    const BNode& top = pool[wide_src[k]];
+    uint32_t ch[8]; int nc = 0;
+    if (top.count) { ch[nc++] = wide_src[k]; }            // a lone leaf (scene of <= 3 triangles)
+    else { ch[nc++] = top.left; ch[nc++] = top.right; }
+    for (;;) {                                            // open the largest inner child until there are 8
+      int best = -1; float best_a = -1.0f;
+      for (int i = 0; i < nc; i++)
+        if (!pool[ch[i]].count) { const float a = pool[ch[i]].box.half_area(); if (a > best_a) { best_a = a; best = i; } }
+      if (best < 0 || nc >= 8) break;
+      const BNode& o = pool[ch[best]];
+      ch[best] = o.left; ch[nc++] = o.right;
+    }
+    // node frame: origin = lower corner of the children's padded boxes, one power-of-two scale per axis
+    Box nb; nb.reset();
+    for (int i = 0; i < nc; i++) nb.grow(pool[ch[i]].box);
+    float p[3]; uint32_t eb[3]; double sc[3];
+    for (int a = 0; a < 3; a++) {
+      p[a] = nb.lo[a] - pad;
+      eb[a] = scale_exp((nb.hi[a] + pad) - p[a] + 2.0f * pad);   // slack for the float rounding of hi + pad - p
+      sc[a] = std::ldexp(1.0, (int)eb[a] - 127);
+    }
+    // slots: a child's slot bits say on which side of the node centre it lies (bit set = upper side), so that
+    // slot ^ (7 ^ ray octant) orders the children near to far; greedy assignment by centroid offset
+    float cen[3] = {0.5f * (nb.lo[0] + nb.hi[0]), 0.5f * (nb.lo[1] + nb.hi[1]), 0.5f * (nb.lo[2] + nb.hi[2])};
+    int slot_of[8]; bool slot_used[8] = {false, false, false, false, false, false, false, false};
+    bool child_done[8] = {false, false, false, false, false, false, false, false};
+    for (int round = 0; round < nc; round++) {
+      int bi = -1, bs = -1; float bv = -std::numeric_limits<float>::infinity();
+      for (int i = 0; i < nc; i++) {
+        if (child_done[i]) continue;
+        const Box& cb = pool[ch[i]].box;
+        const float off[3] = {0.5f * (cb.lo[0] + cb.hi[0]) - cen[0], 0.5f * (cb.lo[1] + cb.hi[1]) - cen[1], 0.5f * (cb.lo[2] + cb.hi[2]) - cen[2]};
+        for (int sl = 0; sl < 8; sl++) {
+          if (slot_used[sl]) continue;
+          const float v = ((sl & 1) ? off[0] : -off[0]) + ((sl & 2) ? off[1] : -off[1]) + ((sl & 4) ? off[2] : -off[2]);
+          if (v > bv) { bv = v; bi = i; bs = sl; }
+        }
+      }
+      slot_of[bi] = bs; slot_used[bs] = true; child_done[bi] = true;
+    }
+    int child_in[8]; for (int sl = 0; sl < 8; sl++) child_in[sl] = -1;
+    for (int i = 0; i < nc; i++) child_in[slot_of[i]] = i;
+
+    uint32_t w[20];
+    for (int i = 0; i < 20; i++) w[i] = 0;
+    uint8_t meta[8] = {0, 0, 0, 0, 0, 0, 0, 0}, qlo[3][8], qhi[3][8];
+    for (int a = 0; a < 3; a++) for (int sl = 0; sl < 8; sl++) { qlo[a][sl] = 255; qhi[a][sl] = 0; }
+    uint32_t imask = 0;
+    const uint32_t child_base = (uint32_t)wide_src.size(), tri_base = (uint32_t)out.tri_src.size();
+    for (int sl = 0; sl < 8; sl++) {
+      const int i = child_in[sl];
+      if (i < 0) continue;
+      const BNode& c = pool[ch[i]];
+      for (int a = 0; a < 3; a++) {   // conservative in exact arithmetic: p + qlo * 2^e <= lo - pad, p + qhi * 2^e >= hi + pad
+        const double lo = (double)(c.box.lo[a] - pad) - (double)p[a], hi = (double)(c.box.hi[a] + pad) - (double)p[a];
+        double ql = std::floor(lo / sc[a]), qh = std::ceil(hi / sc[a]);
+        ql = ql < 0.0 ? 0.0 : (ql > 255.0 ? 255.0 : ql);
+        qh = qh < 0.0 ? 0.0 : (qh > 255.0 ? 255.0 : qh);
+        qlo[a][sl] = (uint8_t)ql; qhi[a][sl] = (uint8_t)qh;
+      }
+      if (c.count) {
+        const uint32_t off = (uint32_t)out.tri_src.size() - tri_base;
+        for (uint32_t t = 0; t < c.count; t++) out.tri_src.push_back(items[c.first + t].id);
+        meta[sl] = (uint8_t)((((1u << c.count) - 1u) << 5) | off);
+      } else {
+        imask |= 1u << sl;
+        meta[sl] = (uint8_t)((1u << 5) | (24u + (uint32_t)sl));
+        wide_src.push_back(ch[i]);
+        wide_depth.push_back(wide_depth[k] + 1);
+      }
+    }
+    w[0] = f2u(p[0]); w[1] = f2u(p[1]); w[2] = f2u(p[2]);
+    w[3] = eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24);
+    w[4] = child_base; w[5] = tri_base;
+    std::memcpy(&w[6], meta, 8);
+    std::memcpy(&w[8], qlo[0], 8); std::memcpy(&w[10], qlo[1], 8); std::memcpy(&w[12], qlo[2], 8);
+    std::memcpy(&w[14], qhi[0], 8); std::memcpy(&w[16], qhi[1], 8); std::memcpy(&w[18], qhi[2], 8);
+    out.nodes.insert(out.nodes.end(), w, w + 20);
+    out.max_depth = std::max(out.max_depth, wide_depth[k]);
   }
-  std::vector<uint32_t> stack{0};
-  while (!stack.empty()) {
-    uint32_t c = stack.back(); stack.pop_back();
-    inner_index[c] = (int32_t)order.size();
-    order.push_back(c);
-    const BNode& nd = pool[c];
-    if (!pool[nd.right].count) stack.push_back(nd.right);
-    if (!pool[nd.left].count) stack.push_back(nd.left);
-  }
-  out.n_nodes = (uint32_t)order.size();
-  out.nodes.resize((size_t)out.n_nodes * 16);
-  for (size_t k = 0; k < order.size(); k++) {
-    const BNode& nd = pool[order[k]];
-    const BNode& c0 = pool[nd.left];
-    const BNode& c1 = pool[nd.right];
-    float* q = out.nodes.data() + k * 16;
-    q[0] = c0.box.lo[0] - pad; q[1] = c0.box.hi[0] + pad; q[2] = c0.box.lo[1] - pad; q[3] = c0.box.hi[1] + pad;
-    q[4] = c1.box.lo[0] - pad; q[5] = c1.box.hi[0] + pad; q[6] = c1.box.lo[1] - pad; q[7] = c1.box.hi[1] + pad;
-    q[8] = c0.box.lo[2] - pad; q[9] = c0.box.hi[2] + pad; q[10] = c1.box.lo[2] - pad; q[11] = c1.box.hi[2] + pad;
-    int32_t a = child_code(pool, nd.left, inner_index), bcode = child_code(pool, nd.right, inner_index);
-    std::memcpy(&q[12], &a, 4); std::memcpy(&q[13], &bcode, 4);
-    q[14] = 0.0f; q[15] = 0.0f;
-  }
+  out.n_nodes = (uint32_t)wide_src.size();
 }
 
 }  // namespace crt

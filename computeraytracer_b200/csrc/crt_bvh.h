@@ -6,10 +6,10 @@
 namespace crt {
 
 struct BvhResult {
-  std::vector<float> nodes;        // 16 floats (4 x float4) per BVH2 node, device layout (crt_device.cuh traverse())
+  std::vector<uint32_t> nodes;     // 20 words (5 x 16 bytes) per 8-wide node, device layout (crt_device.cuh, "Wide8")
   std::vector<uint32_t> tri_src;   // triangle slot (leaf order) -> position in the primitives binding
   uint32_t n_nodes = 0;
-  uint32_t max_depth = 0;
+  uint32_t max_depth = 0;          // depth of the wide tree
   float pad = 0.0f;
   float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};   // padded bounds of all triangles
 };

@@ -25,7 +25,7 @@
 #define CRT_LIN_PARAM_MAX 64            // patches/spheres carried in kernel-parameter (constant-bank) space
 #define CRT_LIGHT_PARAM_MAX 8
 #define CRT_TRI_REF 0x80000000u         // Hit::ref flag: slot in the triangle array
-#define CRT_BVH_STACK 64
+#define CRT_BVH_STACK 32            // node groups: at most one per level of the wide tree
 
 // meta word: category | material << 2 | emission << 4 | reflectance << 16
 #define CRT_META_CAT(m) ((m)&3u)
@@ -66,7 +66,7 @@ struct DevScene {
   // triangles + BVH
   uint32_t n_tri, n_nodes;
   const float4* tri;              // 3 x float4 per triangle, BVH leaf order
-  const float4* nodes;            // 4 x float4 per BVH2 node
+  const uint4* nodes;             // 5 x 16 bytes per 8-wide node ("Wide8" below)
   uint32_t shadow_closest;        // 1: some light's primitive is a triangle -> shadow rays need closest-hit
   float bvh_lo[3], bvh_hi[3];     // padded bounds of all triangles (root box)
   // sharding
@@ -185,92 +185,177 @@ __device__ __forceinline__ bool test_tri(float4 T0, float4 T1, float4 T2, V3 o, 
   return true;
 }
 
-// BVH2 over the triangles.  Node = 4 x float4:
-//   n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)   n1 = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
-//   n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)   n3 = bits(child0, child1, -, -)
-// child >= 0: inner node index; child < 0: leaf, ~child = first_triangle << 3 | (count - 1).
-// Boxes are padded at build time so that culling with (tnear <= best.t) never drops a primitive the
-// linear scan would accept (DESIGN.md "Conservative culling"); equal-t ties go to the higher
-// primitive index, which is what the reference's in-order scan with `t > t_max` rejection yields.
-// Inner-node step: test both children, descend into the nearer one, push the other.  On return `node` is
-// the next node to process (inner >= 0, leaf < 0); returns false when nothing is left (stack empty).
-template <bool STATS>
-__device__ __forceinline__ bool trav_inner(const float4* __restrict__ nodes, V3 o, float idx, float idy, float idz, float t_min,
-                                           const Hit& h, int& node, int& sp, int* stack, Stats& st) {
-  const float4 n0 = __ldg(&nodes[4 * node + 0]);
-  const float4 n1 = __ldg(&nodes[4 * node + 1]);
-  const float4 n2 = __ldg(&nodes[4 * node + 2]);
-  const float4 n3 = __ldg(&nodes[4 * node + 3]);
-  if (STATS) st.node_visits++;
-  float a0 = (n0.x - o.x) * idx, a1 = (n0.y - o.x) * idx;
-  float b0 = (n0.z - o.y) * idy, b1 = (n0.w - o.y) * idy;
-  float c0 = (n2.x - o.z) * idz, c1 = (n2.y - o.z) * idz;
-  const float tn0 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), t_min));
-  const float tf0 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), h.t));
-  a0 = (n1.x - o.x) * idx; a1 = (n1.y - o.x) * idx;
-  b0 = (n1.z - o.y) * idy; b1 = (n1.w - o.y) * idy;
-  c0 = (n2.z - o.z) * idz; c1 = (n2.w - o.z) * idz;
-  const float tn1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), t_min));
-  const float tf1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), h.t));
-  const bool hit0 = tn0 <= tf0, hit1 = tn1 <= tf1;
-  const int ch0 = __float_as_int(n3.x), ch1 = __float_as_int(n3.y);
-  if (hit0 && hit1) {
-    const bool swap = tn1 < tn0;
-    node = swap ? ch1 : ch0;
-    stack[sp++] = swap ? ch0 : ch1;
-    return true;
-  }
-  if (hit0) { node = ch0; return true; }
-  if (hit1) { node = ch1; return true; }
-  if (sp == 0) return false;
-  node = stack[--sp];
-  return true;
+// "Wide8": an 8-wide BVH over the triangles with quantised child boxes (after Ylitie, Karras, Laine, "Efficient incoherent
+// ray traversal on GPUs through compressed wide BVHs", HPG 2017), 80 bytes = 5 x 16-byte words per node:
+//   w0 = (p.x, p.y, p.z, ex | ey << 8 | ez << 16 | imask << 24)     node origin, per-axis scale 2^(e-127), inner-child mask
+//   w1 = (child_base, tri_base, meta[0..3], meta[4..7])
+//   w2 = (qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7])       child box planes: p + q * 2^(e-127), one byte per child
+//   w3 = (qlo.z[0..3], qlo.z[4..7], qhi.x[0..3], qhi.x[4..7])
+//   w4 = (qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7])
+// meta[slot]: 0 = empty; inner child: 1 << 5 | (24 + slot), stored at node child_base + rank among the inner children;
+// leaf: unary triangle count (1, 3, 7) << 5 | offset of its first triangle from tri_base (offset + count <= 24).
+// A child's slot says on which side of the node centre it lies, so slot ^ (7 ^ ray octant) orders children near to far.
+// The quantised planes are conservative in exact arithmetic around boxes that are already padded (crt_bvh.cpp), so culling
+// with (tnear <= tfar), tfar clamped to the best t so far, never drops a primitive the linear scan would accept
+// (DESIGN.md "Conservative culling"); equal-t ties go to the higher primitive index, which is what the reference's in-order
+// scan with `t > t_max` rejection yields.  fminf/fmaxf drop the NaNs of 0 * inf, which only widens an interval.
+#define CRT_WIDE_HITS 0xFF000000u   // group word: bits 24..31 = inner children still to visit (priority order), 0..7 = imask
+
+struct WideRay {     // per-ray constants of the traversal
+  V3 o;
+  float idx, idy, idz;
+  uint32_t octinv;   // 7 ^ octant of the direction
+  bool valid;        // false for a ray with a NaN component: test_tri accepts nothing for it, so there is nothing to traverse
+};
+
+__device__ __forceinline__ WideRay wide_ray(V3 o, V3 d) {
+  WideRay r;
+  r.o = o;
+  // |1/d| is clamped to 1e30: with an infinite reciprocal the plane distances q * (s/d) + (p-o)/d would be inf - inf = NaN,
+  // the axis would drop out of the slab test (still conservative) and an axis-parallel ray would sweep the whole tree.
+  // A finite 1e30 keeps the signs right: both planes on one side of the origin -> miss, origin between them -> all t.
+#ifdef WIDE_NO_CLAMP
+  r.idx = 1.0f / d.x; r.idy = 1.0f / d.y; r.idz = 1.0f / d.z;
+#else
+  r.idx = fminf(fmaxf(1.0f / d.x, -1e30f), 1e30f);
+  r.idy = fminf(fmaxf(1.0f / d.y, -1e30f), 1e30f);
+  r.idz = fminf(fmaxf(1.0f / d.z, -1e30f), 1e30f);
+#endif
+  const uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+  r.octinv = 7u ^ oct;
+#ifdef WIDE_NO_VALID
+  r.valid = true;
+#else
+  r.valid = o.x == o.x && o.y == o.y && o.z == o.z && d.x == d.x && d.y == d.y && d.z == d.z;
+#endif
+  return r;
 }
 
-// Leaf step: test the leaf's triangles under the tie rule.  Returns false when the traversal is over
-// (stack empty, or an any-hit query found its occluder); otherwise `node` is the next node.
+// byte i of an 8-byte plane array as a float, without the (slow-pipe) integer conversion: 0x4B000000 | q is the float
+// 8388608 + q exactly, and subtracting 8388608 is exact
+__device__ __forceinline__ float wide_q(uint32_t lo4, uint32_t hi4, int i) {
+  const uint32_t w = i < 4 ? lo4 : hi4;
+#ifdef WIDE_Q_I2F
+  return (float)((w >> (8 * (i & 3))) & 0xFFu);
+#else
+  const uint32_t sel = 0x7440u | (uint32_t)(i & 3);   // result bytes (3..0) = (0x4B, 0x00, 0x00, w.byte[i & 3])
+  return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f;
+#endif
+}
+
+// Visit one node: slab tests of its 8 children against [t_min, t_max]; returns the node group G (inner children hit, in
+// near-to-far priority bits, plus imask) and the triangle group T (one bit per triangle of the leaf children hit).
+// The reciprocal direction is finite (wide_ray), so its sign says which of a child's two planes per axis is the near one.
 template <bool STATS>
-__device__ __forceinline__ bool trav_leaf(const float4* __restrict__ tris, V3 o, V3 d, uint32_t exclude, float t_min, bool anyhit,
-                                          Hit& h, int& node, int& sp, int* stack, Stats& st) {
-  const uint32_t leaf = (uint32_t)(~node);
-  const uint32_t first = leaf >> 3, count = (leaf & 7u) + 1u;
-  for (uint32_t i = 0; i < count; i++) {
-    const uint32_t slot = first + i;
-    const float4 T0 = __ldg(&tris[3 * slot + 0]);
-    const float4 T1 = __ldg(&tris[3 * slot + 1]);
-    const float4 T2 = __ldg(&tris[3 * slot + 2]);
-    if (STATS) st.tri_tests++;
-    const uint32_t index = __float_as_uint(T0.w);
-    if (index == exclude) continue;
-    float t;
-    if (test_tri(T0, T1, T2, o, d, t_min, h.t, t)) {
-      if (t < h.t || h.idx == CRT_MAX_U32 || index > h.idx) {
-        h.t = t; h.idx = index; h.ref = CRT_TRI_REF | slot;
-        if (anyhit) return false;
-      }
+__device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint32_t node, const WideRay& r, float t_min, float t_max,
+                                          uint2& G, uint2& T, Stats& st) {
+  const uint4 w0 = __ldg(&nodes[5 * node + 0]);
+  const uint4 w1 = __ldg(&nodes[5 * node + 1]);
+  const uint4 w2 = __ldg(&nodes[5 * node + 2]);
+  const uint4 w3 = __ldg(&nodes[5 * node + 3]);
+  const uint4 w4 = __ldg(&nodes[5 * node + 4]);
+  if (STATS) st.node_visits++;
+  const uint32_t imask = w0.w >> 24;
+  // t = ((p + q * s) - o) / d  evaluated as  q * (s / d) + (p - o) / d
+  const float ax = __uint_as_float((w0.w & 0xFFu) << 23) * r.idx;
+  const float ay = __uint_as_float(((w0.w >> 8) & 0xFFu) << 23) * r.idy;
+  const float az = __uint_as_float(((w0.w >> 16) & 0xFFu) << 23) * r.idz;
+  const float bx = (__uint_as_float(w0.x) - r.o.x) * r.idx;
+  const float by = (__uint_as_float(w0.y) - r.o.y) * r.idy;
+  const float bz = (__uint_as_float(w0.z) - r.o.z) * r.idz;
+  // near / far plane arrays per axis (qlo: w2.xy, w2.zw, w3.xy; qhi: w3.zw, w4.xy, w4.zw)
+#ifdef WIDE_NO_SIGNSEL
+  const bool nx = false, ny = false, nz = false;
+#else
+  const bool nx = r.idx < 0.0f, ny = r.idy < 0.0f, nz = r.idz < 0.0f;
+#endif
+  const uint32_t xn0 = nx ? w3.z : w2.x, xn1 = nx ? w3.w : w2.y, xf0 = nx ? w2.x : w3.z, xf1 = nx ? w2.y : w3.w;
+  const uint32_t yn0 = ny ? w4.x : w2.z, yn1 = ny ? w4.y : w2.w, yf0 = ny ? w2.z : w4.x, yf1 = ny ? w2.w : w4.y;
+  const uint32_t zn0 = nz ? w4.z : w3.x, zn1 = nz ? w4.w : w3.y, zf0 = nz ? w3.x : w4.z, zf1 = nz ? w3.y : w4.w;
+  uint32_t hitmask = 0;
+#pragma unroll
+  for (int half = 0; half < 2; half++) {
+    // four meta bytes at a time: bit position and bit pattern each child contributes to the hit mask.  An inner child
+    // (meta = 001 11sss) goes to bit 24 + (slot ^ octinv): near children get the high bits; a leaf puts its unary
+    // triangle count at its triangle offset; an empty child contributes no bits.
+    const uint32_t meta4 = half ? w1.w : w1.z;
+    const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+    const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xFFu;                    // 0xFF in the bytes of inner children
+    const uint32_t bit_index4 = (meta4 ^ ((r.octinv * 0x01010101u) & inner_mask4)) & 0x1F1F1F1Fu;
+    const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int i = half * 4 + j;
+      const float tnx = fmaf(wide_q(xn0, xn1, i), ax, bx), tfx = fmaf(wide_q(xf0, xf1, i), ax, bx);
+      const float tny = fmaf(wide_q(yn0, yn1, i), ay, by), tfy = fmaf(wide_q(yf0, yf1, i), ay, by);
+      const float tnz = fmaf(wide_q(zn0, zn1, i), az, bz), tfz = fmaf(wide_q(zf0, zf1, i), az, bz);
+#ifdef WIDE_NO_SIGNSEL
+      const float tn = fmaxf(fmaxf(fminf(tnx, tfx), fminf(tny, tfy)), fmaxf(fminf(tnz, tfz), t_min));
+      const float tf = fminf(fminf(fmaxf(tnx, tfx), fmaxf(tny, tfy)), fminf(fmaxf(tnz, tfz), t_max));
+#else
+      const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, t_min));
+      const float tf = fminf(fminf(tfx, tfy), fminf(tfz, t_max));
+#endif
+      if (tn <= tf) hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
     }
   }
-  if (sp == 0) return false;
-  node = stack[--sp];
-  return true;
+  G = make_uint2(w1.x, (hitmask & CRT_WIDE_HITS) | imask);
+  T = make_uint2(w1.y, hitmask & ~CRT_WIDE_HITS);
 }
 
+// Take the nearest unvisited inner child out of a node group; returns its node index.
+__device__ __forceinline__ uint32_t wide_pop_child(uint2& G, uint32_t octinv) {
+  const uint32_t b = 31u - (uint32_t)__clz(G.y);
+  G.y &= ~(1u << b);
+  const uint32_t slot = (b - 24u) ^ octinv;
+  return G.x + __popc(G.y & 0xFFu & ((1u << slot) - 1u));
+}
+
+// Test one triangle of a triangle group under the tie rule.  Returns true when an any-hit query has found its occluder.
 template <bool STATS>
-__device__ __forceinline__ bool trav_step(const float4* __restrict__ nodes, const float4* __restrict__ tris, V3 o, V3 d,
-                                          float idx, float idy, float idz, uint32_t exclude, float t_min, bool anyhit,
-                                          Hit& h, int& node, int& sp, int* stack, Stats& st) {
-  if (node >= 0) return trav_inner<STATS>(nodes, o, idx, idy, idz, t_min, h, node, sp, stack, st);
-  return trav_leaf<STATS>(tris, o, d, exclude, t_min, anyhit, h, node, sp, stack, st);
+__device__ __forceinline__ bool wide_tri(const float4* __restrict__ tris, uint2& T, V3 o, V3 d, uint32_t exclude, float t_min, bool anyhit,
+                                         Hit& h, Stats& st) {
+  const uint32_t k = (uint32_t)__ffs(T.y) - 1u;
+  T.y &= T.y - 1u;
+  const uint32_t slot = T.x + k;
+  const float4 T0 = __ldg(&tris[3 * slot + 0]);
+  const float4 T1 = __ldg(&tris[3 * slot + 1]);
+  const float4 T2 = __ldg(&tris[3 * slot + 2]);
+  if (STATS) st.tri_tests++;
+  const uint32_t index = __float_as_uint(T0.w);
+  if (index == exclude) return false;
+  float t;
+  if (test_tri(T0, T1, T2, o, d, t_min, h.t, t)) {
+    if (t < h.t || h.idx == CRT_MAX_U32 || index > h.idx) {
+      h.t = t; h.idx = index; h.ref = CRT_TRI_REF | slot;
+      return anyhit;
+    }
+  }
+  return false;
 }
 
 template <bool ANYHIT, bool STATS>
 __device__ __forceinline__ void traverse(const DevScene& sc, V3 o, V3 d, uint32_t exclude, float t_min, Hit& h, Stats& st) {
   if (sc.n_tri == 0) return;
-  const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
-  int stack[CRT_BVH_STACK];
+  const WideRay r = wide_ray(o, d);
+  if (!r.valid) return;
+  uint2 stack[CRT_BVH_STACK];
   int sp = 0;
-  int node = 0;   // root is always an inner node (a lone leaf is wrapped at build time)
-  while (trav_step<STATS>(sc.nodes, sc.tri, o, d, idx, idy, idz, exclude, t_min, ANYHIT, h, node, sp, stack, st)) {}
+  uint2 G = make_uint2(0u, 0x80000000u);   // the root as the only child of a virtual group
+  for (;;) {
+    uint2 T = make_uint2(0u, 0u);
+    if (G.y & CRT_WIDE_HITS) {
+      const uint32_t node = wide_pop_child(G, r.octinv);
+      if (G.y & CRT_WIDE_HITS) stack[sp++] = G;
+      wide_node<STATS>(sc.nodes, node, r, t_min, h.t, G, T, st);
+    }
+    while (T.y)
+      if (wide_tri<STATS>(sc.tri, T, o, d, exclude, t_min, ANYHIT, h, st)) return;
+    if (!(G.y & CRT_WIDE_HITS)) {
+      if (sp == 0) return;
+      G = stack[--sp];
+    }
+  }
 }
 
 // The patches and spheres, in index order with the reference's sequential semantics (CS:508-515).

@@ -361,7 +361,7 @@ __device__ __forceinline__ void wf_tables(const DevScene& sc, const WfState& w, 
 #define WF_REGEN_MIN_BLOCKS 1
 #endif
 #ifndef WF_TRAV_MIN_BLOCKS
-#define WF_TRAV_MIN_BLOCKS 5
+#define WF_TRAV_MIN_BLOCKS 4
 #endif
 template <bool STATS>
 __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
@@ -585,7 +585,9 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 // a lane that reaches a leaf parks there until the warp switches to the leaf phase, so the (long, rare)
 // triangle tests do not run at one or two lanes on every trip.  Arithmetic per node and per triangle is
 // trav_inner / trav_leaf (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
-#define WF_INNER_MIN_LANES 12
+#ifndef WF_REFILL_MIN
+#define WF_REFILL_MIN 8
+#endif
 template <bool STATS, bool ROUTE>
 __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(const __grid_constant__ DevScene sc, const WfState w, uint32_t it,
                                                         unsigned long long* __restrict__ counters) {
@@ -600,23 +602,27 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t* __restrict__ queue = w.bvh_list;
   uint32_t* fetch = &w.iter[it].n_fetch;
-  const float4* __restrict__ nodes = sc.nodes;
+  const uint4* __restrict__ nodes = sc.nodes;
   const float4* __restrict__ tris = sc.tri;
   const float t_min = sc.t_min;
   Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
 
-  int stack[CRT_BVH_STACK];
-  int node = 0, sp = 0;
+  uint2 stack[CRT_BVH_STACK];
+  int sp = 0;
+  uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);   // node group and triangle group of the lane's ray (crt_device.cuh)
   bool have = false, exhausted = false, anyhit = false;
   uint32_t slot = 0, exclude = CRT_MAX_U32, light_prim = 0;
-  V3 o = v3(0.0f, 0.0f, 0.0f), d = v3(0.0f, 0.0f, 1.0f);
-  float idx = 0.0f, idy = 0.0f, idz = 0.0f;
+  V3 d = v3(0.0f, 0.0f, 1.0f);
+  WideRay r = wide_ray(v3(0.0f, 0.0f, 0.0f), d);
   Hit h; h.t = 0.0f; h.idx = CRT_MAX_U32; h.ref = 0;
 
   for (;;) {
     // ---- refill the lanes that have no ray
+    // (a refill costs the whole warp an atomic round trip plus the loads of the new rays, so it waits until
+    //  WF_REFILL_MIN lanes are idle -- or until nobody has a ray)
     const bool need = !have && !exhausted;
-    const uint32_t mask = __ballot_sync(0xffffffffu, need);
+    uint32_t mask = __ballot_sync(0xffffffffu, need);
+    if (__popc(mask) < WF_REFILL_MIN && __ballot_sync(0xffffffffu, have) != 0u) mask = 0u;
     if (mask) {
       uint32_t base = 0;
       const uint32_t leader = __ffs(mask) - 1u;
@@ -632,7 +638,6 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
           anyhit = (entry & WF_SHADOW_ENTRY) != 0u;
           const float4 a = wf_f4(w, slot, WF_R_S0);
           const uint4 m = wf_u4(w, slot, WF_R_S5);
-          o = v3(a);
           exclude = m.x;
           if (anyhit) {
             // the NEE shadow ray: the light (linear list) is the closest hit so far at distance b.w; any triangle accepted
@@ -646,31 +651,32 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
             d = v3(b);
             h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
           }
-          idx = 1.0f / d.x; idy = 1.0f / d.y; idz = 1.0f / d.z;
-          node = 0; sp = 0;
+          r = wide_ray(v3(a), d);
+          G = make_uint2(0u, r.valid ? 0x80000000u : 0u);   // the root as the only child of a virtual group
+          T = make_uint2(0u, 0u);
+          sp = 0;
           have = true;
         }
       }
     }
     if (__ballot_sync(0xffffffffu, have) == 0u) break;
-    // ---- inner-node phase: lanes at a leaf (node < 0) or without a ray wait
+    // ---- node step, for the lanes whose triangle group is empty: take the nearest unvisited child of the current node
+    //      group (or of the group on top of the stack), fetch it and test its 8 child boxes
     bool done = false;
-    for (;;) {
-      const bool inner = have && !done && node >= 0;
-      const uint32_t m_in = __ballot_sync(0xffffffffu, inner);
-      if (__popc(m_in) < WF_INNER_MIN_LANES) {
-        // too few lanes left here: go test the parked leaves / refill -- unless nobody is parked either
-        const uint32_t m_leaf = __ballot_sync(0xffffffffu, have && !done && node < 0);
-        const uint32_t m_idle = __ballot_sync(0xffffffffu, (!have && !exhausted) || done);
-        if (m_in == 0u || m_leaf != 0u || m_idle != 0u) break;
+    if (have && T.y == 0u) {
+      if (!(G.y & CRT_WIDE_HITS)) {
+        if (sp == 0) done = true;
+        else G = stack[--sp];
       }
-      if (inner) {
-        if (!trav_inner<STATS>(nodes, o, idx, idy, idz, t_min, h, node, sp, stack, st)) done = true;
+      if (!done) {
+        const uint32_t node = wide_pop_child(G, r.octinv);
+        if (G.y & CRT_WIDE_HITS) stack[sp++] = G;
+        wide_node<STATS>(nodes, node, r, t_min, h.t, G, T, st);
       }
     }
-    // ---- leaf phase
-    if (have && !done && node < 0) {
-      if (!trav_leaf<STATS>(tris, o, d, exclude, t_min, anyhit, h, node, sp, stack, st)) done = true;
+    // ---- triangle step: one triangle for every lane that has some left
+    if (have && !done && T.y != 0u) {
+      if (wide_tri<STATS>(tris, T, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
     }
     // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
     //      to the next iteration's shade queue (surface) or finish queue (miss)
