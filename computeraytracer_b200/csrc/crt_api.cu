@@ -306,7 +306,8 @@ int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
   w.finish[0] = (uint32_t*)p; p += 4 * (size_t)n_slots;
   w.finish[1] = (uint32_t*)p; p += 4 * (size_t)n_slots;
   w.regen = (uint32_t*)p; p += 4 * (size_t)n_slots;
-  w.bvh_list = (uint32_t*)p; p += 8 * (size_t)n_slots;
+  w.bvh_list = (uint32_t*)p; p += 4 * (size_t)n_slots;
+  w.shadow_list = (uint32_t*)p; p += 4 * (size_t)n_slots;
   w.iter = (WfIter*)p; p += (size_t)(CRT_WF_MAX_ITERS + 2) * sizeof(WfIter);
   w.work = (uint32_t*)p;
   ctx->wf_slots = n_slots;

@@ -198,7 +198,7 @@ __device__ __forceinline__ bool test_tri(float4 T0, float4 T1, float4 T2, V3 o, 
 // The quantised planes are conservative in exact arithmetic around boxes that are already padded (crt_bvh.cpp), so culling
 // with (tnear <= tfar), tfar clamped to the best t so far, never drops a primitive the linear scan would accept
 // (DESIGN.md "Conservative culling"); equal-t ties go to the higher primitive index, which is what the reference's in-order
-// scan with `t > t_max` rejection yields.  fminf/fmaxf drop the NaNs of 0 * inf, which only widens an interval.
+// scan with `t > t_max` rejection yields.
 #define CRT_WIDE_HITS 0xFF000000u   // group word: bits 24..31 = inner children still to visit (priority order), 0..7 = imask
 
 struct WideRay {     // per-ray constants of the traversal
@@ -214,20 +214,12 @@ __device__ __forceinline__ WideRay wide_ray(V3 o, V3 d) {
   // |1/d| is clamped to 1e30: with an infinite reciprocal the plane distances q * (s/d) + (p-o)/d would be inf - inf = NaN,
   // the axis would drop out of the slab test (still conservative) and an axis-parallel ray would sweep the whole tree.
   // A finite 1e30 keeps the signs right: both planes on one side of the origin -> miss, origin between them -> all t.
-#ifdef WIDE_NO_CLAMP
-  r.idx = 1.0f / d.x; r.idy = 1.0f / d.y; r.idz = 1.0f / d.z;
-#else
   r.idx = fminf(fmaxf(1.0f / d.x, -1e30f), 1e30f);
   r.idy = fminf(fmaxf(1.0f / d.y, -1e30f), 1e30f);
   r.idz = fminf(fmaxf(1.0f / d.z, -1e30f), 1e30f);
-#endif
   const uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
   r.octinv = 7u ^ oct;
-#ifdef WIDE_NO_VALID
-  r.valid = true;
-#else
   r.valid = o.x == o.x && o.y == o.y && o.z == o.z && d.x == d.x && d.y == d.y && d.z == d.z;
-#endif
   return r;
 }
 
@@ -235,12 +227,8 @@ __device__ __forceinline__ WideRay wide_ray(V3 o, V3 d) {
 // 8388608 + q exactly, and subtracting 8388608 is exact
 __device__ __forceinline__ float wide_q(uint32_t lo4, uint32_t hi4, int i) {
   const uint32_t w = i < 4 ? lo4 : hi4;
-#ifdef WIDE_Q_I2F
-  return (float)((w >> (8 * (i & 3))) & 0xFFu);
-#else
   const uint32_t sel = 0x7440u | (uint32_t)(i & 3);   // result bytes (3..0) = (0x4B, 0x00, 0x00, w.byte[i & 3])
   return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f;
-#endif
 }
 
 // Visit one node: slab tests of its 8 children against [t_min, t_max]; returns the node group G (inner children hit, in
@@ -264,11 +252,7 @@ __device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint3
   const float by = (__uint_as_float(w0.y) - r.o.y) * r.idy;
   const float bz = (__uint_as_float(w0.z) - r.o.z) * r.idz;
   // near / far plane arrays per axis (qlo: w2.xy, w2.zw, w3.xy; qhi: w3.zw, w4.xy, w4.zw)
-#ifdef WIDE_NO_SIGNSEL
-  const bool nx = false, ny = false, nz = false;
-#else
   const bool nx = r.idx < 0.0f, ny = r.idy < 0.0f, nz = r.idz < 0.0f;
-#endif
   const uint32_t xn0 = nx ? w3.z : w2.x, xn1 = nx ? w3.w : w2.y, xf0 = nx ? w2.x : w3.z, xf1 = nx ? w2.y : w3.w;
   const uint32_t yn0 = ny ? w4.x : w2.z, yn1 = ny ? w4.y : w2.w, yf0 = ny ? w2.z : w4.x, yf1 = ny ? w2.w : w4.y;
   const uint32_t zn0 = nz ? w4.z : w3.x, zn1 = nz ? w4.w : w3.y, zf0 = nz ? w3.x : w4.z, zf1 = nz ? w3.y : w4.w;
@@ -289,13 +273,8 @@ __device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint3
       const float tnx = fmaf(wide_q(xn0, xn1, i), ax, bx), tfx = fmaf(wide_q(xf0, xf1, i), ax, bx);
       const float tny = fmaf(wide_q(yn0, yn1, i), ay, by), tfy = fmaf(wide_q(yf0, yf1, i), ay, by);
       const float tnz = fmaf(wide_q(zn0, zn1, i), az, bz), tfz = fmaf(wide_q(zf0, zf1, i), az, bz);
-#ifdef WIDE_NO_SIGNSEL
-      const float tn = fmaxf(fmaxf(fminf(tnx, tfx), fminf(tny, tfy)), fmaxf(fminf(tnz, tfz), t_min));
-      const float tf = fminf(fminf(fmaxf(tnx, tfx), fmaxf(tny, tfy)), fminf(fmaxf(tnz, tfz), t_max));
-#else
       const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, t_min));
       const float tf = fminf(fminf(tfx, tfy), fminf(tfz, t_max));
-#endif
       if (tn <= tf) hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
     }
   }

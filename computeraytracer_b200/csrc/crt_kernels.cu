@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(CRT_BLOCK) pt_megakernel(const __grid_constant
       if (split) s += (sc.rank + sc.world - ((s - 1u) % sc.world)) % sc.world;
       if (s <= s_end) {
         s_cur = s;
-        path_begin<STATS>(sc, px, py, s, ps, rng, st);
+        path_begin<STATS, false>(sc, px, py, s, ps, rng, st);
         n_paths++;
         alive = true;
       } else {
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(CRT_BLOCK) pt_megakernel(const __grid_constant
             have_pixel = true;
             if (s <= s_end) {
               s_cur = s;
-              path_begin<STATS>(sc, px, py, s, ps, rng, st);
+              path_begin<STATS, false>(sc, px, py, s, ps, rng, st);
               n_paths++;
               alive = true;
             } else {

@@ -142,9 +142,12 @@ __device__ __forceinline__ bool path_consume(const DevScene& sc, const float* __
 }
 
 // seed + camera_ray + sample_wavelengths + path_trace's initial state, CS:98-101, 121-131
-template <bool STATS>
+// TEA_TAB: seed lane w from the per-pixel table (wavefront kernels, which wait on memory anyway) or hashed here (the
+// megakernel is FP32/issue-bound on linear-list scenes: the dependent load cost it 5 %).
+template <bool STATS, bool TEA_TAB>
 __device__ __forceinline__ void path_begin(const DevScene& sc, uint32_t px, uint32_t py, uint32_t sample, PathState& ps, Rng& rng, Stats& st) {
-  rng.x = py; rng.y = px * 100u; rng.z = sample; rng.w = __ldg(&sc.tea_tab[px + py * sc.W]);   // CS:98 (tea_tab_kernel)
+  rng.x = py; rng.y = px * 100u; rng.z = sample;
+  rng.w = TEA_TAB ? __ldg(&sc.tea_tab[px + py * sc.W]) : tea(px, py * 100u);   // CS:98
   const float G = (float)sc.grid_size;
   const float cell = (float)(sample % sc.grid_size);
   const float s = ((float)px + (cell + rnd(rng)) / G) / (float)sc.W;            // CS:497

@@ -46,7 +46,6 @@ __device__ __forceinline__ uint4& wf_u4(const WfState& w, uint32_t slot, int wor
 #define WF_FLAG_TRANSMISSION 2u
 #define WF_FLAG_PENDING 4u            // an NEE contribution (S7) waits for the any-hit answer of its shadow ray (S6)
 #define WF_FLAG_DEAD 8u               // Russian roulette ended the path; only the pending contribution is outstanding
-#define WF_SHADOW_ENTRY 0x80000000u   // BVH queue entry: the slot's shadow ray (otherwise its extension ray)
 
 // unit -> pixel: units enumerate this rank's 8x4 tiles, 32 pixels each (the megakernel's unit order)
 __device__ __forceinline__ bool unit_pixel(const DevScene& sc, uint32_t unit, uint32_t& px, uint32_t& py) {
@@ -330,11 +329,11 @@ __device__ __forceinline__ void wf_emit(const DevScene& sc, const WfState& w, ui
   const PushTicket tb = wf_reserve(to_bounce, &w.iter[it + 1u].n_bounce);
   const PushTicket tf = wf_reserve(to_finish, &w.iter[it + 1u].n_finish);
   const PushTicket tq = wf_reserve(want_bvh, &w.iter[it].n_bvh);
-  const PushTicket ts = wf_reserve(shadow, &w.iter[it].n_bvh);
+  const PushTicket ts = wf_reserve(shadow, &w.iter[it].n_shadow);
   wf_commit(tb, to_bounce, slot, nx ? w.bounce[1] : w.bounce[0]);
   wf_commit(tf, to_finish, slot, nx ? w.finish[1] : w.finish[0]);
   wf_commit(tq, want_bvh, slot, w.bvh_list);
-  wf_commit(ts, shadow, slot | WF_SHADOW_ENTRY, w.bvh_list);
+  wf_commit(ts, shadow, slot, w.shadow_list);
   lc.n_bvh_rays += (want_bvh ? 1u : 0u) + (shadow ? 1u : 0u);
 }
 
@@ -459,7 +458,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
           const uint32_t j = wid / ck.n_units;
           uint32_t px, py;
           if (unit_pixel(sc, wid - j * ck.n_units, px, py)) {   // edge tiles have units outside the image
-            path_begin<STATS>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
+            path_begin<STATS, true>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
             lc.n_paths++;
             alive = true;
             need = false;
@@ -537,7 +536,7 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ Dev
           const uint32_t j = wid / ck.n_units;
           uint32_t px, py;
           if (unit_pixel(sc, wid - j * ck.n_units, px, py)) {   // edge tiles have units outside the image
-            path_begin<STATS>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
+            path_begin<STATS, true>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
             lc.n_paths++;
             alive = true; has_ext = true; flags = 0; nee.pending = false;
             need = false;
@@ -581,10 +580,11 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 
 // Persistent traversal of the BVH queue of iteration `it`.  Each lane owns one ray at a time; when its
 // traversal ends it writes the hit back and takes the next queue entry, so the warp never waits for its
-// slowest ray.  While-while form: the warp keeps stepping inner nodes as long as enough lanes have one;
-// a lane that reaches a leaf parks there until the warp switches to the leaf phase, so the (long, rare)
-// triangle tests do not run at one or two lanes on every trip.  Arithmetic per node and per triangle is
-// trav_inner / trav_leaf (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
+// slowest ray.  Every trip of the loop is one node step (fetch an 8-wide node, test its child boxes) for the lanes
+// whose triangle group is empty, then one triangle test for the lanes that have triangles pending.  (Batching the
+// triangle tests until 6..24 lanes have some was measured 35-85 % slower: the kernel lives on overlapping the
+// node and triangle fetches of different lanes.)  Arithmetic per node and per triangle is wide_node / wide_tri
+// (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
 #ifndef WF_REFILL_MIN
 #define WF_REFILL_MIN 8
 #endif
@@ -592,7 +592,8 @@ template <bool STATS, bool ROUTE>
 __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(const __grid_constant__ DevScene sc, const WfState w, uint32_t it,
                                                         unsigned long long* __restrict__ counters) {
   __shared__ uint32_t s_done[WF_BLOCK / 32][2][64];
-  const uint32_t n = w.iter[it].n_bvh;
+  const uint32_t n_ext = w.iter[it].n_bvh;
+  const uint32_t n = n_ext + w.iter[it].n_shadow;   // one fetch cursor over both queues: extension rays first
   if (n == 0) return;
   DoneBuf db_b, db_f;
   db_b.buf = s_done[threadIdx.x >> 5][0]; db_b.n = 0;
@@ -633,9 +634,8 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
         if (q >= n) {
           exhausted = true;
         } else {
-          const uint32_t entry = queue[q];
-          slot = entry & ~WF_SHADOW_ENTRY;
-          anyhit = (entry & WF_SHADOW_ENTRY) != 0u;
+          anyhit = q >= n_ext;
+          slot = anyhit ? w.shadow_list[q - n_ext] : queue[q];
           const float4 a = wf_f4(w, slot, WF_R_S0);
           const uint4 m = wf_u4(w, slot, WF_R_S5);
           exclude = m.x;

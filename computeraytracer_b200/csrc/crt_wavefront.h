@@ -12,9 +12,10 @@ struct WfIter {
   uint32_t n_bounce;   // slots whose extension ray hit a surface: wf_shade
   uint32_t n_finish;   // slots whose path is over (miss, or only an NEE answer was outstanding): wf_regen finishes them
   uint32_t n_regen;    // slots freed by wf_shade in this iteration: wf_regen starts new paths on them
-  uint32_t n_bvh;      // rays queued for the BVH in this iteration
+  uint32_t n_bvh;      // extension rays queued for the BVH in this iteration
   uint32_t n_fetch;    // wf_traverse's fetch cursor into the BVH queue
-  uint32_t pad[3];
+  uint32_t n_shadow;   // NEE shadow rays queued for the BVH in this iteration (traversed after the extension rays)
+  uint32_t pad[2];
 };
 
 #define CRT_WF_REC_WORDS 10     // 16-byte words per slot record (160 bytes = 5 DRAM sectors); layout in crt_wavefront.cu
@@ -25,7 +26,8 @@ struct WfState {
   uint32_t* bounce[2]; // shade queue of this / the next iteration
   uint32_t* finish[2]; // finish queue of this / the next iteration
   uint32_t* regen;     // slots freed by wf_shade in the current iteration
-  uint32_t* bvh_list;  // [2 * slots] rays that must traverse the BVH: slot, or slot | 1 << 31 for its shadow ray
+  uint32_t* bvh_list;  // [slots] slots whose extension ray must traverse the BVH
+  uint32_t* shadow_list; // [slots] slots whose NEE shadow ray must (kept apart so that warps hold rays of one kind)
   WfIter* iter;        // [CRT_WF_MAX_ITERS + 2]
   uint32_t* work;      // next unassigned (sample, pixel) work item of the chunk
   uint32_t tables_in_smem;

@@ -58,7 +58,8 @@ def main():
     hdr = blk["rows"][0]
     data = blk["rows"][1:]
     ci = {n: i for i, n in enumerate(hdr)}
-    mangled = ksub.replace("<(bool)", "ILb").replace(">", "")
+    m_ = re.match(r"(\w+)<(.*)>", ksub)
+    mangled = (m_.group(1) + "I" + "".join("Lb" + a.strip().replace("(bool)", "") + "E" for a in m_.group(2).split(","))) if m_ else ksub
     sass = sass_lines(mangled if "Lb" in mangled else "pt_megakernelILb0" if "megakernel" in ksub else mangled)
     if len(sass) != len(data):
         print(f"warning: {len(sass)} disassembled instructions vs {len(data)} profiled rows", file=sys.stderr)
