@@ -19,6 +19,8 @@ namespace {
 
 constexpr int kBins = 32;
 constexpr uint32_t kLeafMax = 3;         // a wide node's meta byte holds the leaf's triangle count in 3 unary bits
+constexpr uint32_t kBvh2LeafMax = 1;     // the binary tree is split down to single triangles; the collapse decides the leaves
+constexpr float kNodeCost = 1.0f, kPrimCost = 0.3f;   // SAH weights of the collapse (Ylitie et al. 2017, section 4.1)
 constexpr uint32_t kForceMedianDepth = 36;
 constexpr float kTraversalCost = 1.0f;   // relative to one triangle test
 
@@ -36,7 +38,7 @@ struct Box {
   }
 };
 
-struct BNode { Box box; uint32_t left = 0, right = 0, first = 0, count = 0; };
+struct BNode { Box box; uint32_t left = 0, right = 0, first = 0, count = 0, total = 0; };   // count != 0: BVH2 leaf; total: triangles below
 
 struct Builder {
   std::vector<Item>& items;
@@ -65,9 +67,9 @@ struct Builder {
       float c[3] = {0.5f * (it.lo[0] + it.hi[0]), 0.5f * (it.lo[1] + it.hi[1]), 0.5f * (it.lo[2] + it.hi[2])};
       cbox.grow(c, c);
     }
-    n.box = box; n.first = first; n.count = 0;
+    n.box = box; n.first = first; n.count = 0; n.total = count;
     note_depth(depth);
-    if (count <= 2) { n.count = count; return; }
+    if (count <= kBvh2LeafMax) { n.count = count; return; }
 
     uint32_t mid = 0;
     bool have_split = false;
@@ -100,7 +102,7 @@ struct Builder {
       if (best_axis >= 0) {
         const float pa = box.half_area();
         const float split_cost = kTraversalCost + (pa > 0.0f ? best_cost / pa : 0.0f);
-        if (count <= kLeafMax && (float)count <= split_cost) { n.count = count; return; }
+        if (count <= kBvh2LeafMax && (float)count <= split_cost) { n.count = count; return; }
         const float c0 = cbox.lo[best_axis], scale = (float)kBins / (cbox.hi[best_axis] - cbox.lo[best_axis]);
         const int ax = best_axis, bin = best_bin;
         Item* b = items.data() + first;
@@ -114,7 +116,7 @@ struct Builder {
       }
     }
     if (!have_split) {
-      if (count <= kLeafMax && depth < kForceMedianDepth) { n.count = count; return; }
+      if (count <= kBvh2LeafMax && depth < kForceMedianDepth) { n.count = count; return; }
       // object median along the widest centroid axis (also the fallback for coincident centroids)
       int ax = 0;
       float e0 = cbox.hi[0] - cbox.lo[0], e1 = cbox.hi[1] - cbox.lo[1], e2 = cbox.hi[2] - cbox.lo[2];
@@ -187,24 +189,60 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
   b.build(0, 0, (uint32_t)n, 0);
   const std::vector<BNode>& pool = b.pool;
 
+  // ---- which BVH2 subtrees become wide nodes, which become leaves: the SAH-optimal collapse of Ylitie et al. (2017,
+  // section 4.1) by dynamic programming.  cost[n][i-1] = cheapest way to represent the subtree of n as at most i
+  // children of a wide node (i = 1: one child, either a leaf of <= 3 triangles or a wide node of its own).
+  const uint32_t n_bvh2 = b.next.load();
+  std::vector<float> cost((size_t)n_bvh2 * 7);
+  std::vector<uint8_t> dec((size_t)n_bvh2 * 8);   // [0..6]: split for i = 1..7 (0 = "same as i-1"; for i = 1: 0 = leaf, else split of the wide node); 
+  const float inf = std::numeric_limits<float>::infinity();
+  for (uint32_t k = n_bvh2; k-- > 0;) {           // children are allocated after their parent: reverse order is post-order
+    const BNode& nd = pool[k];
+    float* c = &cost[(size_t)k * 7];
+    uint8_t* dk = &dec[(size_t)k * 8];
+    const float area = nd.box.half_area();
+    const float leaf = nd.total <= kLeafMax ? area * (float)nd.total * kPrimCost : inf;
+    if (nd.count) { for (int i = 0; i < 7; i++) { c[i] = leaf; dk[i] = 0; } continue; }
+    const float* cl = &cost[(size_t)nd.left * 7];
+    const float* cr = &cost[(size_t)nd.right * 7];
+    float best = inf; int best_k = 1;
+    for (int j = 1; j <= 7; j++) { const float v = cl[j - 1] + cr[7 - j]; if (v < best) { best = v; best_k = j; } }   // j + (8-j) = 8 slots
+    const float internal = best + area * kNodeCost;
+    if (leaf <= internal) { c[0] = leaf; dk[0] = 0; } else { c[0] = internal; dk[0] = (uint8_t)best_k; }
+    for (int i = 2; i <= 7; i++) {
+      float v = c[i - 2]; int vk = 0;
+      for (int j = 1; j < i; j++) { const float u = cl[j - 1] + cr[i - j - 1]; if (u < v) { v = u; vk = j; } }
+      c[i - 1] = v; dk[i - 1] = (uint8_t)vk;
+    }
+  }
+  // the children of BVH2 subtree n when it may occupy up to i slots
+  struct Collect {
+    const std::vector<BNode>& pool; const std::vector<uint8_t>& dec;
+    void run(uint32_t n, int i, uint32_t* out, int& nc) const {
+      while (i > 1 && dec[(size_t)n * 8 + (i - 1)] == 0) i--;
+      if (i == 1 || pool[n].count) { out[nc++] = n; return; }
+      const int j = dec[(size_t)n * 8 + (i - 1)];
+      run(pool[n].left, j, out, nc);
+      run(pool[n].right, i - j, out, nc);
+    }
+  } collect{pool, dec};
+  auto is_leaf_child = [&](uint32_t n) { return pool[n].count != 0 || dec[(size_t)n * 8] == 0; };
+
   // Wide nodes are created breadth-first: the inner children of a node get consecutive indices (child_base + rank in
   // slot order), its leaf children's triangles consecutive slots from tri_base (offset + count <= 24).
   std::vector<uint32_t> wide_src{0};      // wide node -> BVH2 node it was collapsed from
   std::vector<uint32_t> wide_depth{1};
   out.tri_src.reserve(n);
-  out.nodes.reserve((n / 2 + 16) * 20);
+  out.nodes.reserve((n / 4 + 16) * 20);
   for (size_t k = 0; k < wide_src.size(); k++) {
     const BNode& top = pool[wide_src[k]];
     uint32_t ch[8]; int nc = 0;
-    if (top.count) { ch[nc++] = wide_src[k]; }            // a lone leaf (scene of <= 3 triangles)
-    else { ch[nc++] = top.left; ch[nc++] = top.right; }
-    for (;;) {                                            // open the largest inner child until there are 8
-      int best = -1; float best_a = -1.0f;
-      for (int i = 0; i < nc; i++)
-        if (!pool[ch[i]].count) { const float a = pool[ch[i]].box.half_area(); if (a > best_a) { best_a = a; best = i; } }
-      if (best < 0 || nc >= 8) break;
-      const BNode& o = pool[ch[best]];
-      ch[best] = o.left; ch[nc++] = o.right;
+    if (top.count || (k == 0 && dec[0] == 0)) {
+      ch[nc++] = wide_src[k];                              // the whole scene is one leaf (<= 3 triangles)
+    } else {
+      const int j = dec[(size_t)wide_src[k] * 8];          // the split the wide node of this subtree was costed with
+      collect.run(top.left, j, ch, nc);
+      collect.run(top.right, 8 - j, ch, nc);
     }
     // node frame: origin = lower corner of the children's padded boxes, one power-of-two scale per axis
     Box nb; nb.reset();
@@ -254,10 +292,10 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
         qh = qh < 0.0 ? 0.0 : (qh > 255.0 ? 255.0 : qh);
         qlo[a][sl] = (uint8_t)ql; qhi[a][sl] = (uint8_t)qh;
       }
-      if (c.count) {
+      if (is_leaf_child(ch[i])) {
         const uint32_t off = (uint32_t)out.tri_src.size() - tri_base;
-        for (uint32_t t = 0; t < c.count; t++) out.tri_src.push_back(items[c.first + t].id);
-        meta[sl] = (uint8_t)((((1u << c.count) - 1u) << 5) | off);
+        for (uint32_t t = 0; t < c.total; t++) out.tri_src.push_back(items[c.first + t].id);   // a subtree's items are contiguous
+        meta[sl] = (uint8_t)((((1u << c.total) - 1u) << 5) | off);
       } else {
         imask |= 1u << sl;
         meta[sl] = (uint8_t)((1u << 5) | (24u + (uint32_t)sl));
