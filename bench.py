@@ -329,10 +329,13 @@ def run_b200(args):
                 "note": "algorithmic bytes = " + what + "; fetches served by L1/L2 count, so they exceed DRAM traffic "
                         "when the scene is L2-resident (see DESIGN.md section 6)"}
     prof = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(prof):
+    if os.path.exists(prof):   # ncu-measured DRAM bytes per ray of this kernel (see the file), scaled to this run's launches
         try:
             with open(prof) as f:
-                roofline["traffic"] = json.load(f).get(args.workload, {}).get(kernel)
+                per_ray = json.load(f).get(args.workload, {}).get(kernel, {}).get("dram_bytes_per_ray")
+            if per_ray is not None and args.width == 1920 and args.height == 1080:
+                roofline["traffic"] = per_ray * my_rays / max(k_n, 1)
+                roofline["traffic_source"] = "profiles/r01_traffic.json (ncu launch list, cold L2 per launch)"
         except Exception:
             pass
 

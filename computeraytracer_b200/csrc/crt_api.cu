@@ -339,6 +339,9 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   // guards: staging <= ~8 GB, work items of a chunk < 2^31
   while (chunk > 1 && ((uint64_t)n_pixels * chunk * 16ull > (8ull << 30) || (uint64_t)n_units * chunk >= (1ull << 31))) chunk--;
   const bool split_spp = ctx->shard_mode == CRT_SHARD_SPLIT_SPP && ctx->world > 1;
+  // under split-spp a rank renders every world-th frame: size the chunk by the frames this rank renders, not by the
+  // frame numbers it spans (8 ranks with 64-frame chunks ran 8 samples per chunk: the pool half empty, 8x the tails)
+  if (split_spp) chunk = (uint32_t)std::min<uint64_t>((uint64_t)chunk * ctx->world, 1u << 20);
   uint32_t left = n;
   while (left) {
     const uint32_t k = left < chunk ? left : chunk;
