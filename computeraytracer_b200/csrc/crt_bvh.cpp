@@ -147,16 +147,17 @@ struct WideChild { uint32_t bvh2; float c[3]; };
 
 inline uint32_t f2u(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 
-// exponent e with 2^e >= ext / 255, as the biased byte of a float (so the device builds 2^e with one shift)
-inline uint32_t scale_exp(float ext) {
+// exponent e of the quantisation step, 2^e >= ext / 255, clamped so that both 2^e and 2^(e+15) are normal floats (the node
+// stores the biased exponent of 2^15 * step: the device builds that factor with one shift, crt_device.cuh wide_node)
+inline int scale_exp(float ext) {
   int e = -126;
   if (ext > 0.0f) {
     e = (int)std::ceil(std::log2((double)ext / 255.0));
     while (std::ldexp(255.0, e) < (double)ext) e++;   // guard against log2 rounding
     if (e < -126) e = -126;
-    if (e > 127) e = 127;
+    if (e > 112) e = 112;
   }
-  return (uint32_t)(e + 127);
+  return e;
 }
 
 }  // namespace
@@ -247,11 +248,12 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
     // node frame: origin = lower corner of the children's padded boxes, one power-of-two scale per axis
     Box nb; nb.reset();
     for (int i = 0; i < nc; i++) nb.grow(pool[ch[i]].box);
-    float p[3]; uint32_t eb[3]; double sc[3];
+    float p[3]; uint32_t eb[3]; double sc[3];   // eb: biased exponent of 2^15 * step
     for (int a = 0; a < 3; a++) {
       p[a] = nb.lo[a] - pad;
-      eb[a] = scale_exp((nb.hi[a] + pad) - p[a] + 2.0f * pad);   // slack for the float rounding of hi + pad - p
-      sc[a] = std::ldexp(1.0, (int)eb[a] - 127);
+      const int e = scale_exp((nb.hi[a] + pad) - p[a] + 2.0f * pad);   // slack for the float rounding of hi + pad - p
+      eb[a] = (uint32_t)(e + 15 + 127);
+      sc[a] = std::ldexp(1.0, e);
     }
     // slots: a child's slot bits say on which side of the node centre it lies (bit set = upper side), so that
     // slot ^ (7 ^ ray octant) orders the children near to far; greedy assignment by centroid offset

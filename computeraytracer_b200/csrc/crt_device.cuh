@@ -90,7 +90,24 @@ __device__ __forceinline__ V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y +
 __device__ __forceinline__ V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
 __device__ __forceinline__ V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
 __device__ __forceinline__ V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ V3 operator/(V3 a, float s) { return v3(a.x / s, a.y / s, a.z / s); }
+// a / b, IEEE-rounded like the plain operator (the build sets -prec-div=true).  ptxas's division sends a zero numerator to
+// its slow path, a subroutine of ~40 instructions that the whole warp waits for; zeros are common here (components of
+// axis-aligned normals, clamped cosines, the XYZ of a path that found no light: ncu counted 10 slow-path calls per warp
+// and bounce, 12 % of wf_logic's instructions).  0 / b is a zero with the sign of a ^ b for every b that is neither zero
+// nor NaN, so those lanes divide 1 / b on the fast path and the zero is selected afterwards.
+#ifndef CRT_DIV_SHORTCUT
+#define CRT_DIV_SHORTCUT 1
+#endif
+__device__ __forceinline__ float crt_div(float a, float b) {
+#if CRT_DIV_SHORTCUT
+  const bool z = a == 0.0f && fabsf(b) > 0.0f;   // false for b = 0 and b = NaN: those take the plain division
+  const float q = (z ? 1.0f : a) / b;
+  return z ? __uint_as_float((__float_as_uint(a) ^ __float_as_uint(b)) & 0x80000000u) : q;
+#else
+  return a / b;
+#endif
+}
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return v3(crt_div(a.x, s), crt_div(a.y, s), crt_div(a.z, s)); }
 __device__ __forceinline__ float dot(V3 a, V3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
 __device__ __forceinline__ V3 cross(V3 a, V3 b) {
   return v3(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));
@@ -141,7 +158,7 @@ __device__ __forceinline__ void test_lin(const LinPrim& p, uint32_t slot, V3 o, 
     // CS:541-546: flipping the normal negates n.d exactly, so |n.d| and the quotient below are unchanged
     if (fabsf(ndotd) < 0.0001f) return;
     V3 p0 = v3(p.B);
-    float t = dot(n, p0 - o) / ndotd;                // CS:554
+    float t = crt_div(dot(n, p0 - o), ndotd);        // CS:554
     if (t < t_min || t > h.t) return;                // CS:557
     V3 m = madd(o, t, d) - p0;                       // CS:561-562
     float u = dot(m, v3(p.C)) / p.C.w;               // CS:563
@@ -187,9 +204,9 @@ __device__ __forceinline__ bool test_tri(float4 T0, float4 T1, float4 T2, V3 o, 
 
 // "Wide8": an 8-wide BVH over the triangles with quantised child boxes (after Ylitie, Karras, Laine, "Efficient incoherent
 // ray traversal on GPUs through compressed wide BVHs", HPG 2017), 80 bytes = 5 x 16-byte words per node:
-//   w0 = (p.x, p.y, p.z, ex | ey << 8 | ez << 16 | imask << 24)     node origin, per-axis scale 2^(e-127), inner-child mask
+//   w0 = (p.x, p.y, p.z, ex | ey << 8 | ez << 16 | imask << 24)     node origin, per-axis step s = 2^(e-127-15), inner-child mask
 //   w1 = (child_base, tri_base, meta[0..3], meta[4..7])
-//   w2 = (qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7])       child box planes: p + q * 2^(e-127), one byte per child
+//   w2 = (qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7])       child box planes: p + q * s, one byte per child
 //   w3 = (qlo.z[0..3], qlo.z[4..7], qhi.x[0..3], qhi.x[4..7])
 //   w4 = (qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7])
 // meta[slot]: 0 = empty; inner child: 1 << 5 | (24 + slot), stored at node child_base + rank among the inner children;
@@ -211,32 +228,42 @@ struct WideRay {     // per-ray constants of the traversal
 __device__ __forceinline__ WideRay wide_ray(V3 o, V3 d) {
   WideRay r;
   r.o = o;
-  // |1/d| is clamped to 1e30: with an infinite reciprocal the plane distances q * (s/d) + (p-o)/d would be inf - inf = NaN,
+  // |1/d| is clamped to 1e18: with an infinite reciprocal the plane distances q * (s/d) + (p-o)/d would be inf - inf = NaN,
   // the axis would drop out of the slab test (still conservative) and an axis-parallel ray would sweep the whole tree.
-  // A finite 1e30 keeps the signs right: both planes on one side of the origin -> miss, origin between them -> all t.
-  r.idx = fminf(fmaxf(1.0f / d.x, -1e30f), 1e30f);
-  r.idy = fminf(fmaxf(1.0f / d.y, -1e30f), 1e30f);
-  r.idz = fminf(fmaxf(1.0f / d.z, -1e30f), 1e30f);
+  // A finite bound keeps the signs right: both planes on one side of the origin -> miss, origin between them -> all t
+  // (the planes are at least the padding away from any accepted hit, and padding * 1e18 exceeds every t of a scene);
+  // 1e18 leaves room for the factor 2^15 s of wide_node below FLT_MAX.
+  r.idx = fminf(fmaxf(1.0f / d.x, -1e18f), 1e18f);
+  r.idy = fminf(fmaxf(1.0f / d.y, -1e18f), 1e18f);
+  r.idz = fminf(fmaxf(1.0f / d.z, -1e18f), 1e18f);
   const uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
   r.octinv = 7u ^ oct;
   r.valid = o.x == o.x && o.y == o.y && o.z == o.z && d.x == d.x && d.y == d.y && d.z == d.z;
   return r;
 }
 
-// byte i of an 8-byte plane array as a float, without the (slow-pipe) integer conversion: 0x4B000000 | q is the float
-// 8388608 + q exactly, and subtracting 8388608 is exact
-__device__ __forceinline__ float wide_q(uint32_t lo4, uint32_t hi4, int i) {
+// byte i of an 8-byte plane array as the float f = 1 + q * 2^-15: the byte is dropped into bits 8..15 of the mantissa of
+// 1.0f by one PRMT, and t = (p + q*s - o)/d is evaluated as f * (2^15 s/d) + ((p - o)/d - 2^15 s/d) by one FFMA.  (Going
+// through 8388608 + q and subtracting costs an FADD per plane -- 48 per node -- and the integer conversion runs on the
+// slow pipe.)  `one` is 0x3F800000 in a register the compiler cannot see through (wide_one): with a literal there, ptxas
+// puts the literal in PRMT's third operand and re-materialises the selector in a register before every PRMT.
+// Rounding: b' = b - a' loses at most 2^-24 |a'| = 2^-9 quantisation steps; a step is at most 2/255 of the node's extent,
+// so the planes move by less than 2^-16 of the scene's extent, half of the padding the boxes were built with
+// (crt_bvh.cpp: pad = extent / 32768), which leaves the culling conservative (DESIGN.md "Conservative culling").
+__device__ __forceinline__ uint32_t wide_one(uint32_t runtime_below_2_31) { return 0x3F800000u | (runtime_below_2_31 >> 31); }
+
+__device__ __forceinline__ float wide_q(uint32_t lo4, uint32_t hi4, int i, uint32_t one) {
   const uint32_t w = i < 4 ? lo4 : hi4;
-  const uint32_t sel = 0x7440u | (uint32_t)(i & 3);   // result bytes (3..0) = (0x4B, 0x00, 0x00, w.byte[i & 3])
-  return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f;
+  const uint32_t sel = 0x7604u | ((uint32_t)(i & 3) << 4);   // result bytes (3..0) = (0x3F, 0x80, w.byte[i & 3], 0x00)
+  return __uint_as_float(__byte_perm(w, one, sel));
 }
 
 // Visit one node: slab tests of its 8 children against [t_min, t_max]; returns the node group G (inner children hit, in
 // near-to-far priority bits, plus imask) and the triangle group T (one bit per triangle of the leaf children hit).
 // The reciprocal direction is finite (wide_ray), so its sign says which of a child's two planes per axis is the near one.
 template <bool STATS>
-__device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint32_t node, const WideRay& r, float t_min, float t_max,
-                                          uint2& G, uint2& T, Stats& st) {
+__device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint32_t node, const WideRay& r, uint32_t one, float t_min,
+                                          float t_max, uint2& G, uint2& T, Stats& st) {
   const uint4 w0 = __ldg(&nodes[5 * node + 0]);
   const uint4 w1 = __ldg(&nodes[5 * node + 1]);
   const uint4 w2 = __ldg(&nodes[5 * node + 2]);
@@ -244,13 +271,14 @@ __device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint3
   const uint4 w4 = __ldg(&nodes[5 * node + 4]);
   if (STATS) st.node_visits++;
   const uint32_t imask = w0.w >> 24;
-  // t = ((p + q * s) - o) / d  evaluated as  q * (s / d) + (p - o) / d
+  // t = ((p + q * s) - o) / d  evaluated as  (1 + q 2^-15) * (2^15 s / d) + ((p - o) / d - 2^15 s / d); the node stores the
+  // exponent of 2^15 s
   const float ax = __uint_as_float((w0.w & 0xFFu) << 23) * r.idx;
   const float ay = __uint_as_float(((w0.w >> 8) & 0xFFu) << 23) * r.idy;
   const float az = __uint_as_float(((w0.w >> 16) & 0xFFu) << 23) * r.idz;
-  const float bx = (__uint_as_float(w0.x) - r.o.x) * r.idx;
-  const float by = (__uint_as_float(w0.y) - r.o.y) * r.idy;
-  const float bz = (__uint_as_float(w0.z) - r.o.z) * r.idz;
+  const float bx = (__uint_as_float(w0.x) - r.o.x) * r.idx - ax;
+  const float by = (__uint_as_float(w0.y) - r.o.y) * r.idy - ay;
+  const float bz = (__uint_as_float(w0.z) - r.o.z) * r.idz - az;
   // near / far plane arrays per axis (qlo: w2.xy, w2.zw, w3.xy; qhi: w3.zw, w4.xy, w4.zw)
   const bool nx = r.idx < 0.0f, ny = r.idy < 0.0f, nz = r.idz < 0.0f;
   const uint32_t xn0 = nx ? w3.z : w2.x, xn1 = nx ? w3.w : w2.y, xf0 = nx ? w2.x : w3.z, xf1 = nx ? w2.y : w3.w;
@@ -270,9 +298,9 @@ __device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint3
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int i = half * 4 + j;
-      const float tnx = fmaf(wide_q(xn0, xn1, i), ax, bx), tfx = fmaf(wide_q(xf0, xf1, i), ax, bx);
-      const float tny = fmaf(wide_q(yn0, yn1, i), ay, by), tfy = fmaf(wide_q(yf0, yf1, i), ay, by);
-      const float tnz = fmaf(wide_q(zn0, zn1, i), az, bz), tfz = fmaf(wide_q(zf0, zf1, i), az, bz);
+      const float tnx = fmaf(wide_q(xn0, xn1, i, one), ax, bx), tfx = fmaf(wide_q(xf0, xf1, i, one), ax, bx);
+      const float tny = fmaf(wide_q(yn0, yn1, i, one), ay, by), tfy = fmaf(wide_q(yf0, yf1, i, one), ay, by);
+      const float tnz = fmaf(wide_q(zn0, zn1, i, one), az, bz), tfz = fmaf(wide_q(zf0, zf1, i, one), az, bz);
       const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, t_min));
       const float tf = fminf(fminf(tfx, tfy), fminf(tfz, t_max));
       if (tn <= tf) hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
@@ -321,12 +349,13 @@ __device__ __forceinline__ void traverse(const DevScene& sc, V3 o, V3 d, uint32_
   uint2 stack[CRT_BVH_STACK];
   int sp = 0;
   uint2 G = make_uint2(0u, 0x80000000u);   // the root as the only child of a virtual group
+  const uint32_t one = wide_one(sc.n_tri);
   for (;;) {
     uint2 T = make_uint2(0u, 0u);
     if (G.y & CRT_WIDE_HITS) {
       const uint32_t node = wide_pop_child(G, r.octinv);
       if (G.y & CRT_WIDE_HITS) stack[sp++] = G;
-      wide_node<STATS>(sc.nodes, node, r, t_min, h.t, G, T, st);
+      wide_node<STATS>(sc.nodes, node, r, one, t_min, h.t, G, T, st);
     }
     while (T.y)
       if (wide_tri<STATS>(sc.tri, T, o, d, exclude, t_min, ANYHIT, h, st)) return;
@@ -348,10 +377,21 @@ __device__ __forceinline__ Hit scan_linear(const DevScene& sc, V3 o, V3 d, uint3
   return h;
 }
 
+#ifndef CRT_FAST_ROOT_RCP
+#define CRT_FAST_ROOT_RCP 1
+#endif
 // Can the ray reach any triangle at all within [t_min, best]?  Same conservative slab test as a node's.
 __device__ __forceinline__ bool hits_root_box(const DevScene& sc, V3 o, V3 d, float best) {
   if (sc.n_tri == 0) return false;
+#if CRT_FAST_ROOT_RCP
+  // approximate reciprocals (1 ulp): the bounds are padded by 2^-15 of the scene's extent, the test only has to be conservative
+  float idx, idy, idz;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(idx) : "f"(d.x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(idy) : "f"(d.y));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(idz) : "f"(d.z));
+#else
   const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
+#endif
   float a0 = (sc.bvh_lo[0] - o.x) * idx, a1 = (sc.bvh_hi[0] - o.x) * idx;
   float b0 = (sc.bvh_lo[1] - o.y) * idy, b1 = (sc.bvh_hi[1] - o.y) * idy;
   float c0 = (sc.bvh_lo[2] - o.z) * idz, c1 = (sc.bvh_hi[2] - o.z) * idz;
@@ -498,7 +538,7 @@ __device__ __forceinline__ V3 spectral_to_xyz(const float* __restrict__ cie, flo
   for (int k = 0; k < 3; k++) {
     const float* c = cie + 471 * k + 40;
     float s = fmaf(c[lam[3]], L.w, fmaf(c[lam[2]], L.z, fmaf(c[lam[1]], L.y, c[lam[0]] * L.x)));
-    o[k] = (s * 300.0f) / 427.42758f;
+    o[k] = crt_div(s * 300.0f, 427.42758f);
   }
   return v3(o[0], o[1], o[2]);
 }

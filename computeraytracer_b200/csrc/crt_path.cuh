@@ -107,9 +107,9 @@ __device__ __forceinline__ bool path_consume(const DevScene& sc, const float* __
     if (h.idx == include) {
       const Surface sh = surface_of(sc, h, ps.o, ps.d);
       const float pdf_l = compute_light_pdf(sc, CRT_META_EMIS(sh.meta), sh.normal, sh.position, ps.o, ps.d);  // CS:393
-      const float pdf_b = cos_theta / CRT_PI_F;
+      const float pdf_b = crt_div(cos_theta, CRT_PI_F);
       const float w = power_heuristic(pdf_l, pdf_b);
-      le = make_float4(le.x * w / pdf_l, le.y * w / pdf_l, le.z * w / pdf_l, le.w * w / pdf_l);  // CS:400
+      le = make_float4(crt_div(le.x * w, pdf_l), crt_div(le.y * w, pdf_l), crt_div(le.z * w, pdf_l), crt_div(le.w * w, pdf_l));  // CS:400
     } else {
       le = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                                // CS:407
     }

@@ -182,9 +182,9 @@ __device__ __forceinline__ int wf_bounce(const DevScene& sc, const float* __rest
     if (hs.idx == include) {
       const Surface sh = surface_of(sc, hs, s.position, light_dir);
       const float pdf_l = compute_light_pdf(sc, CRT_META_EMIS(sh.meta), sh.normal, sh.position, s.position, light_dir);  // CS:393
-      const float pdf_b = cos_theta / CRT_PI_F;
+      const float pdf_b = crt_div(cos_theta, CRT_PI_F);
       const float w = power_heuristic(pdf_l, pdf_b);
-      le = make_float4(le.x * w / pdf_l, le.y * w / pdf_l, le.z * w / pdf_l, le.w * w / pdf_l);  // CS:400
+      le = make_float4(crt_div(le.x * w, pdf_l), crt_div(le.y * w, pdf_l), crt_div(le.z * w, pdf_l), crt_div(le.w * w, pdf_l));  // CS:400
       if (hits_root_box(sc, s.position, light_dir, hs.t)) {   // a triangle may still occlude: any-hit query bounded by the light
         add_now = false;
         nee.pending = true; nee.d = light_dir; nee.t = hs.t; nee.light_prim = include;
@@ -475,7 +475,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
 
 // wf_logic: the single-kernel form of wf_shade + wf_regen.  One thread per live slot: add the pending NEE answer, shade the
 // hit (wf_bounce), and if the path ended finish it and start the slot's next path right here.  Lanes of a warp are in
-// different phases (ncu: ~14 of 32 active), but these kernels wait on memory and on dependent arithmetic rather than on
+// different phases (ncu: ~17 of 32 active), but these kernels wait on memory and on dependent arithmetic rather than on
 // issue slots, and the fused form makes one pass over a slot's record per bounce instead of up to two.
 template <bool STATS>
 __global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
@@ -580,10 +580,11 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 
 // Persistent traversal of the BVH queue of iteration `it`.  Each lane owns one ray at a time; when its
 // traversal ends it writes the hit back and takes the next queue entry, so the warp never waits for its
-// slowest ray.  Every trip of the loop is one node step (fetch an 8-wide node, test its child boxes) for the lanes
-// whose triangle group is empty, then one triangle test for the lanes that have triangles pending.  (Batching the
-// triangle tests until 6..24 lanes have some was measured 35-85 % slower: the kernel lives on overlapping the
-// node and triangle fetches of different lanes.)  Arithmetic per node and per triangle is wide_node / wide_tri
+// slowest ray.  Every trip of the loop is one triangle test for the lanes that have triangles pending, then one node
+// step (fetch an 8-wide node, test its child boxes) for the lanes whose triangle group is empty by then.  (Measured:
+// triangles first is 4 % faster than nodes first; batching the triangle tests until 6..24 lanes have some is 35-85 %
+// slower -- the kernel lives on overlapping the node and triangle fetches of different lanes; prefetch.global.L1 of the
+// next node or triangle changes nothing.)  Arithmetic per node and per triangle is wide_node / wide_tri
 // (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
 #ifndef WF_REFILL_MIN
 #define WF_REFILL_MIN 8
@@ -606,6 +607,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
   const uint4* __restrict__ nodes = sc.nodes;
   const float4* __restrict__ tris = sc.tri;
   const float t_min = sc.t_min;
+  const uint32_t one = wide_one(it);
   Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
 
   uint2 stack[CRT_BVH_STACK];
@@ -660,10 +662,14 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
       }
     }
     if (__ballot_sync(0xffffffffu, have) == 0u) break;
-    // ---- node step, for the lanes whose triangle group is empty: take the nearest unvisited child of the current node
-    //      group (or of the group on top of the stack), fetch it and test its 8 child boxes
+    // ---- triangle step: one triangle for every lane that has some left
     bool done = false;
-    if (have && T.y == 0u) {
+    if (have && T.y != 0u) {
+      if (wide_tri<STATS>(tris, T, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
+    }
+    // ---- node step, for the lanes whose triangle group is (now) empty: take the nearest unvisited child of the current
+    //      node group (or of the group on top of the stack), fetch it and test its 8 child boxes
+    if (have && !done && T.y == 0u) {
       if (!(G.y & CRT_WIDE_HITS)) {
         if (sp == 0) done = true;
         else G = stack[--sp];
@@ -671,12 +677,8 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
       if (!done) {
         const uint32_t node = wide_pop_child(G, r.octinv);
         if (G.y & CRT_WIDE_HITS) stack[sp++] = G;
-        wide_node<STATS>(nodes, node, r, t_min, h.t, G, T, st);
+        wide_node<STATS>(nodes, node, r, one, t_min, h.t, G, T, st);
       }
-    }
-    // ---- triangle step: one triangle for every lane that has some left
-    if (have && !done && T.y != 0u) {
-      if (wide_tri<STATS>(tris, T, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
     }
     // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
     //      to the next iteration's shade queue (surface) or finish queue (miss)
