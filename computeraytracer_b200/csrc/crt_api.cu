@@ -296,7 +296,8 @@ int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
   if (ctx->wf_mem && ctx->wf_slots >= n_slots) return CRT_OK;
   if (ctx->wf_mem) { cudaFree(ctx->wf_mem); ctx->wf_mem = nullptr; }
   // one record per slot; shade and finish queues of two iterations, the regen queue, the BVH queue (2 entries per slot)
-  const size_t total = (size_t)(CRT_WF_REC_WORDS * 16 + 7 * 4) * n_slots + kWfCounterBytes + 256;
+  const size_t slow_bytes = (size_t)(1 + 3 * CRT_WF_SLOW_RAYS) * 16;
+  const size_t total = (size_t)(CRT_WF_REC_WORDS * 16 + 7 * 4) * n_slots + kWfCounterBytes + 256 + slow_bytes;
   CU(cudaMalloc(&ctx->wf_mem, total));
   uint8_t* p = (uint8_t*)ctx->wf_mem;
   WfState& w = ctx->wf;
@@ -309,7 +310,13 @@ int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
   w.bvh_list = (uint32_t*)p; p += 4 * (size_t)n_slots;
   w.shadow_list = (uint32_t*)p; p += 4 * (size_t)n_slots;
   w.iter = (WfIter*)p; p += (size_t)(CRT_WF_MAX_ITERS + 2) * sizeof(WfIter);
-  w.work = (uint32_t*)p;
+  w.work = (uint32_t*)p; p += 256;
+  w.slow = (float4*)p;
+  CU(cudaMemset(w.slow, 0, slow_bytes));
+  {
+    const char* e = getenv("CRT_SLOW_RAY_NODES");   // diagnostics: log rays that visit at least this many nodes (stats mode)
+    w.slow_min = e ? (uint32_t)strtoul(e, nullptr, 10) : 0u;
+  }
   ctx->wf_slots = n_slots;
   if (!ctx->wf_host_count) CU(cudaMallocHost(&ctx->wf_host_count, 8));
   return CRT_OK;
@@ -724,6 +731,20 @@ int crt_get_counters(crt_ctx* ctx, uint64_t* out, size_t n) {
   tmp[CRT_CNT_LAUNCHES] = ctx->launches;
   tmp[CRT_CNT_WF_ITERATIONS] = ctx->wf_iterations;
   for (size_t i = 0; i < n; i++) out[i] = tmp[i];
+  if (ctx->wf_mem && ctx->wf.slow_min) {   // diagnostics: print and clear the slow-ray log (CRT_SLOW_RAY_NODES)
+    static float4 log[1 + 3 * CRT_WF_SLOW_RAYS];
+    CU(cudaMemcpy(log, ctx->wf.slow, sizeof(log), cudaMemcpyDeviceToHost));
+    uint32_t cnt; memcpy(&cnt, &log[0].x, 4);
+    fprintf(stderr, "[libcrt] %u rays visited >= %u BVH nodes\n", cnt, ctx->wf.slow_min);
+    for (uint32_t k = 0; k < cnt && k < CRT_WF_SLOW_RAYS; k++) {
+      const float4 a = log[1 + 3 * k], b = log[2 + 3 * k], c = log[3 + 3 * k];
+      uint32_t it, nodes, excl, any, slot, tris;
+      memcpy(&it, &a.w, 4); memcpy(&nodes, &b.w, 4); memcpy(&excl, &c.x, 4); memcpy(&any, &c.y, 4); memcpy(&slot, &c.z, 4); memcpy(&tris, &c.w, 4);
+      fprintf(stderr, "[libcrt] slow ray: o=(%.9g, %.9g, %.9g) d=(%.9g, %.9g, %.9g) exclude=%u anyhit=%u iteration=%u nodes=%u triangles=%u slot=%u\n",
+              a.x, a.y, a.z, b.x, b.y, b.z, excl, any, it, nodes, tris, slot);
+    }
+    CU(cudaMemset(ctx->wf.slow, 0, 16));
+  }
   return CRT_OK;
 }
 

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <future>
 #include <limits>
@@ -20,7 +21,8 @@ namespace {
 constexpr int kBins = 32;
 constexpr uint32_t kLeafMax = 3;         // a wide node's meta byte holds the leaf's triangle count in 3 unary bits
 constexpr uint32_t kBvh2LeafMax = 1;     // the binary tree is split down to single triangles; the collapse decides the leaves
-constexpr float kNodeCost = 1.0f, kPrimCost = 0.3f;   // SAH weights of the collapse (Ylitie et al. 2017, section 4.1)
+constexpr float kNodeCost = 1.0f;        // SAH weights of the collapse (Ylitie et al. 2017, section 4.1); the triangle weight
+constexpr float kPrimCostDefault = 0.75f; // (measured 0.3 .. 1.5 on mesh1m and soup10m: flat above 0.75; 0.3 is 1 % / 5 % slower); tuning override: CRT_BVH_PRIM_COST
 constexpr uint32_t kForceMedianDepth = 36;
 constexpr float kTraversalCost = 1.0f;   // relative to one triangle test
 
@@ -194,6 +196,8 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
   // section 4.1) by dynamic programming.  cost[n][i-1] = cheapest way to represent the subtree of n as at most i
   // children of a wide node (i = 1: one child, either a leaf of <= 3 triangles or a wide node of its own).
   const uint32_t n_bvh2 = b.next.load();
+  float kPrimCost = kPrimCostDefault;
+  if (const char* e = std::getenv("CRT_BVH_PRIM_COST")) { const float v = std::strtof(e, nullptr); if (v > 0.0f) kPrimCost = v; }
   std::vector<float> cost((size_t)n_bvh2 * 7);
   std::vector<uint8_t> dec((size_t)n_bvh2 * 8);   // [0..6]: split for i = 1..7 (0 = "same as i-1"; for i = 1: 0 = leaf, else split of the wide node); 
   const float inf = std::numeric_limits<float>::infinity();

@@ -618,6 +618,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
   V3 d = v3(0.0f, 0.0f, 1.0f);
   WideRay r = wide_ray(v3(0.0f, 0.0f, 0.0f), d);
   Hit h; h.t = 0.0f; h.idx = CRT_MAX_U32; h.ref = 0;
+  uint32_t ray_nodes = 0, ray_tris = 0, max_nodes = 0;   // STATS: per-ray visit counts
 
   for (;;) {
     // ---- refill the lanes that have no ray
@@ -658,6 +659,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
           T = make_uint2(0u, 0u);
           sp = 0;
           have = true;
+          ray_nodes = ray_tris = 0;
         }
       }
     }
@@ -665,6 +667,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     // ---- triangle step: one triangle for every lane that has some left
     bool done = false;
     if (have && T.y != 0u) {
+      if (STATS) ray_tris++;
       if (wide_tri<STATS>(tris, T, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
     }
     // ---- node step, for the lanes whose triangle group is (now) empty: take the nearest unvisited child of the current
@@ -678,11 +681,23 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
         const uint32_t node = wide_pop_child(G, r.octinv);
         if (G.y & CRT_WIDE_HITS) stack[sp++] = G;
         wide_node<STATS>(nodes, node, r, one, t_min, h.t, G, T, st);
+        if (STATS) ray_nodes++;
       }
     }
     // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
     //      to the next iteration's shade queue (surface) or finish queue (miss)
     const bool fin_ext = done && !anyhit;
+    if (STATS && done) {
+      max_nodes = max(max_nodes, ray_nodes);
+      if (w.slow_min && ray_nodes >= w.slow_min) {
+        const uint32_t k = atomicAdd(reinterpret_cast<uint32_t*>(w.slow), 1u);
+        if (k < CRT_WF_SLOW_RAYS) {
+          w.slow[1 + 3 * k] = make_float4(r.o.x, r.o.y, r.o.z, __uint_as_float(it));
+          w.slow[2 + 3 * k] = make_float4(d.x, d.y, d.z, __uint_as_float(ray_nodes));
+          w.slow[3 + 3 * k] = make_float4(__uint_as_float(exclude), __uint_as_float(anyhit ? 1u : 0u), __uint_as_float(slot), __uint_as_float(ray_tris));
+        }
+      }
+    }
     if (done) {
       if (anyhit) {
         if (h.idx != light_prim) reinterpret_cast<float*>(&wf_f4(w, slot, WF_R_S6))[3] = -1.0f;   // occluded
@@ -707,6 +722,8 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
       for (int s = 16; s > 0; s >>= 1) x += __shfl_down_sync(0xffffffffu, x, s);
       if (lane == 0 && x) atomicAdd(&counters[CRT_CNT_NODE_VISITS + k], x);
     }
+    for (int s = 16; s > 0; s >>= 1) max_nodes = max(max_nodes, __shfl_down_sync(0xffffffffu, max_nodes, s));
+    if (lane == 0) atomicMax(&counters[CRT_CNT_MAX_RAY_NODES], (unsigned long long)max_nodes);
   }
 }
 

@@ -18,6 +18,7 @@ struct WfIter {
   uint32_t pad[2];
 };
 
+#define CRT_WF_SLOW_RAYS 64
 #define CRT_WF_REC_WORDS 10     // 16-byte words per slot record (160 bytes = 5 DRAM sectors); layout in crt_wavefront.cu
 #define WF_REC_WORDS CRT_WF_REC_WORDS
 
@@ -31,6 +32,8 @@ struct WfState {
   WfIter* iter;        // [CRT_WF_MAX_ITERS + 2]
   uint32_t* work;      // next unassigned (sample, pixel) work item of the chunk
   uint32_t tables_in_smem;
+  uint32_t slow_min;   // diagnostics (CRT_SLOW_RAY_NODES, stats builds): log rays that visit at least this many BVH nodes; 0 = off
+  float4* slow;        // [1 + 3 * CRT_WF_SLOW_RAYS]: word 0 = count, then (origin, iteration), (direction, nodes), (exclude, anyhit, slot, triangles)
 };
 
 // One chunk of frames rendered as a wavefront.

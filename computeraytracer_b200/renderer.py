@@ -29,7 +29,8 @@ LIB_PATH = os.environ.get("CRT_LIBCRT") or os.path.join(_HERE, "libcrt.so")   # 
 
 NUM_COUNTERS = 16
 COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits", "tri_tests", "rand",
-                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum", "launches", "wf_iterations", "bvh_rays"]
+                 "term_miss", "term_rr", "term_light", "term_depth", "depth_sum", "launches", "wf_iterations", "bvh_rays",
+                 "max_ray_nodes"]
 SHARD_NONE, SHARD_TILES, SHARD_SPLIT_SPP = 0, 1, 2
 KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
 FLAG_STATS, FLAG_KERNEL_TIMES, FLAG_WF_SPLIT = 1, 2, 4

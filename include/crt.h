@@ -110,8 +110,10 @@ enum crt_counter {
   CRT_CNT_DEPTH_SUM = 11,   /* sum over paths of depth at termination                     */
   CRT_CNT_LAUNCHES = 12,    /* hot-path kernel launches (counted on the host)             */
   CRT_CNT_WF_ITERATIONS = 13, /* wavefront iterations (one ray per live path each)        */
-  CRT_CNT_BVH_RAYS = 14     /* wavefront: rays queued for BVH traversal (the rest are settled
+  CRT_CNT_BVH_RAYS = 14,    /* wavefront: rays queued for BVH traversal (the rest are settled
                                by the linear list and the root-box test)                  */
+  CRT_CNT_MAX_RAY_NODES = 15  /* wavefront, CRT_FLAG_STATS: most BVH nodes visited by one ray (a maximum,
+                               not a sum)                                                   */
 };
 
 /* requestAdapter/requestDevice + pipeline creation (MJ:8-9, MJ:535-543).  Fails with
