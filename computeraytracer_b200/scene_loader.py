@@ -55,6 +55,15 @@ PATCH_DTYPE = np.dtype(
 )
 
 
+def copy_records(a, dtype=None) -> np.ndarray:
+    """A writable copy of a record array (or of its raw bytes) that keeps every byte, padding lanes included:
+    ndarray.copy() / .tobytes() on a padded structured dtype go field by field and leave the padding undefined."""
+    if isinstance(a, np.ndarray):
+        dtype = dtype or a.dtype
+        a = np.ascontiguousarray(a).view(np.uint8).tobytes()
+    return np.frombuffer(bytearray(a), dtype=dtype)
+
+
 @dataclass
 class PackedScene:
     """The byte buffers of one scene, keyed like the shader's bindings."""
@@ -70,13 +79,18 @@ class PackedScene:
     spectrum_index: Dict[str, int] = field(default_factory=dict)
 
     def bindings(self) -> Dict[int, bytes]:
+        # the raw bytes of the record arrays: ndarray.tobytes() on a padded structured dtype copies field by field and
+        # leaves the padding lanes of the copy uninitialised, which made the uploaded bytes (and any digest of them)
+        # differ from run to run
+        def raw(a: np.ndarray) -> bytes:
+            return np.ascontiguousarray(a).view(np.uint8).tobytes()
         return {
-            3: self.planar_patches.tobytes(),
+            3: raw(self.planar_patches),
             4: self.camera.tobytes(),
             5: self.cie.tobytes(),
             6: self.spectra.tobytes(),
-            7: self.lights.tobytes(),
-            8: self.primitives.tobytes(),
+            7: raw(self.lights),
+            8: raw(self.primitives),
         }
 
     @property

@@ -14,7 +14,7 @@ from typing import Optional
 
 import numpy as np
 
-from .scene_loader import (CATEGORY_TRIANGLE, PATCH_DTYPE, PRIM_DTYPE, PackedScene)
+from .scene_loader import (CATEGORY_TRIANGLE, PATCH_DTYPE, PRIM_DTYPE, PackedScene, copy_records)
 
 _DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "default_scene.npz")
 
@@ -31,12 +31,12 @@ def default_scene(width: Optional[int] = None, height: Optional[int] = None) -> 
     return PackedScene(
         width=int(cam[11]),
         height=int(cam[12]),
-        planar_patches=np.frombuffer(z["planar_patches"].tobytes(), dtype=PATCH_DTYPE).copy(),
+        planar_patches=copy_records(z["planar_patches"].tobytes(), PATCH_DTYPE),
         camera=cam,
         cie=z["cie"].astype("<f4"),
         spectra=z["spectra"].astype("<f4"),
-        lights=np.frombuffer(z["lights"].tobytes(), dtype=PRIM_DTYPE).copy(),
-        primitives=np.frombuffer(z["primitives"].tobytes(), dtype=PRIM_DTYPE).copy(),
+        lights=copy_records(z["lights"].tobytes(), PRIM_DTYPE),
+        primitives=copy_records(z["primitives"].tobytes(), PRIM_DTYPE),
         spectrum_index={n: i for i, n in enumerate(names)},
     )
 
@@ -58,9 +58,9 @@ def _with_triangles(base: PackedScene, keep: int, tris: np.ndarray, reflectance:
     prims["data4"][sl, 3] = np.arange(keep, keep + n, dtype=np.uint32)
     return PackedScene(
         width=base.width, height=base.height,
-        planar_patches=base.planar_patches[:keep].copy(),
+        planar_patches=copy_records(base.planar_patches[:keep]),
         camera=base.camera.copy(), cie=base.cie, spectra=base.spectra,
-        lights=base.lights.copy(), primitives=prims, spectrum_index=dict(base.spectrum_index),
+        lights=copy_records(base.lights), primitives=prims, spectrum_index=dict(base.spectrum_index),
     )
 
 

@@ -93,8 +93,8 @@ class OracleScene:
         self.lib = orc.lib
         self.params = Params.from_buffer_copy(bytes(params))   # accepts the product's Params struct too (same layout)
         self.W, self.H = int(ps.camera[11]), int(ps.camera[12])
-        self._prims = np.frombuffer(ps.primitives.tobytes(), dtype=np.uint8).copy()
-        self._lights = np.frombuffer(ps.lights.tobytes(), dtype=np.uint8).copy()
+        self._prims = np.frombuffer(ps.bindings()[8], dtype=np.uint8).copy()
+        self._lights = np.frombuffer(ps.bindings()[7], dtype=np.uint8).copy()
         self._cam = np.ascontiguousarray(ps.camera, dtype=np.float32).copy()
         self._cie = np.ascontiguousarray(ps.cie, dtype=np.float32).copy()
         self._spec = np.ascontiguousarray(ps.spectra, dtype=np.float32).copy()
