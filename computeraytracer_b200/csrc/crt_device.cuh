@@ -262,13 +262,8 @@ __device__ __forceinline__ float wide_q(uint32_t lo4, uint32_t hi4, int i, uint3
 // near-to-far priority bits, plus imask) and the triangle group T (one bit per triangle of the leaf children hit).
 // The reciprocal direction is finite (wide_ray), so its sign says which of a child's two planes per axis is the near one.
 template <bool STATS>
-__device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint32_t node, const WideRay& r, uint32_t one, float t_min,
-                                          float t_max, uint2& G, uint2& T, Stats& st) {
-  const uint4 w0 = __ldg(&nodes[5 * node + 0]);
-  const uint4 w1 = __ldg(&nodes[5 * node + 1]);
-  const uint4 w2 = __ldg(&nodes[5 * node + 2]);
-  const uint4 w3 = __ldg(&nodes[5 * node + 3]);
-  const uint4 w4 = __ldg(&nodes[5 * node + 4]);
+__device__ __forceinline__ void wide_node_eval(const uint4 w0, const uint4 w1, const uint4 w2, const uint4 w3, const uint4 w4, const WideRay& r,
+                                               uint32_t one, float t_min, float t_max, uint2& G, uint2& T, Stats& st) {
   if (STATS) st.node_visits++;
   const uint32_t imask = w0.w >> 24;
   // t = ((p + q * s) - o) / d  evaluated as  (1 + q 2^-15) * (2^15 s / d) + ((p - o) / d - 2^15 s / d); the node stores the
@@ -310,6 +305,17 @@ __device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint3
   T = make_uint2(w1.y, hitmask & ~CRT_WIDE_HITS);
 }
 
+template <bool STATS>
+__device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint32_t node, const WideRay& r, uint32_t one, float t_min,
+                                          float t_max, uint2& G, uint2& T, Stats& st) {
+  const uint4 w0 = __ldg(&nodes[5 * node + 0]);
+  const uint4 w1 = __ldg(&nodes[5 * node + 1]);
+  const uint4 w2 = __ldg(&nodes[5 * node + 2]);
+  const uint4 w3 = __ldg(&nodes[5 * node + 3]);
+  const uint4 w4 = __ldg(&nodes[5 * node + 4]);
+  wide_node_eval<STATS>(w0, w1, w2, w3, w4, r, one, t_min, t_max, G, T, st);
+}
+
 // Take the nearest unvisited inner child out of a node group; returns its node index.
 __device__ __forceinline__ uint32_t wide_pop_child(uint2& G, uint32_t octinv) {
   const uint32_t b = 31u - (uint32_t)__clz(G.y);
@@ -317,6 +323,10 @@ __device__ __forceinline__ uint32_t wide_pop_child(uint2& G, uint32_t octinv) {
   const uint32_t slot = (b - 24u) ^ octinv;
   return G.x + __popc(G.y & 0xFFu & ((1u << slot) - 1u));
 }
+
+template <bool STATS>
+__device__ __forceinline__ bool wide_tri_eval(const float4 T0, const float4 T1, const float4 T2, uint32_t slot, V3 o, V3 d, uint32_t exclude,
+                                              float t_min, bool anyhit, Hit& h, Stats& st);
 
 // Test one triangle of a triangle group under the tie rule.  Returns true when an any-hit query has found its occluder.
 template <bool STATS>
@@ -328,6 +338,13 @@ __device__ __forceinline__ bool wide_tri(const float4* __restrict__ tris, uint2&
   const float4 T0 = __ldg(&tris[3 * slot + 0]);
   const float4 T1 = __ldg(&tris[3 * slot + 1]);
   const float4 T2 = __ldg(&tris[3 * slot + 2]);
+  return wide_tri_eval<STATS>(T0, T1, T2, slot, o, d, exclude, t_min, anyhit, h, st);
+}
+
+// The test of wide_tri on a triangle that has been fetched already (slot = its position in the leaf-ordered array).
+template <bool STATS>
+__device__ __forceinline__ bool wide_tri_eval(const float4 T0, const float4 T1, const float4 T2, uint32_t slot, V3 o, V3 d, uint32_t exclude,
+                                              float t_min, bool anyhit, Hit& h, Stats& st) {
   if (STATS) st.tri_tests++;
   const uint32_t index = __float_as_uint(T0.w);
   if (index == exclude) return false;

@@ -584,7 +584,8 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 // step (fetch an 8-wide node, test its child boxes) for the lanes whose triangle group is empty by then.  (Measured:
 // triangles first is 4 % faster than nodes first; batching the triangle tests until 6..24 lanes have some is 35-85 %
 // slower -- the kernel lives on overlapping the node and triangle fetches of different lanes; prefetch.global.L1 of the
-// next node or triangle changes nothing.)  Arithmetic per node and per triangle is wide_node / wide_tri
+// next node or triangle changes nothing; one merged fetch phase per trip -- triangle lanes and node lanes load through the
+// same registers and the warp waits once -- is equal on mesh1m and 5 % slower on the 10M soup.)  Arithmetic per node and per triangle is wide_node / wide_tri
 // (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
 #ifndef WF_REFILL_MIN
 #define WF_REFILL_MIN 8
