@@ -41,6 +41,10 @@ SHADE_PASS_BYTES = 232  # wf_shade per slot: S0..S5 + H read (112) and written (
 QUEUE_RAY_BYTES = 84  # wf_traverse per queued ray: queue entry 4 + origin 16 + direction 16 + exclude word 16 + hit read 16 + hit write 16
 
 
+# frames per step = the samples per pixel BASELINE.json quotes for the config (configs[2], [1], [4])
+CONFIG_SPP = {"mesh1m": 256, "cornell": 64, "soup10m": 16}
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -48,7 +52,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="mesh1m", choices=["mesh1m", "cornell", "soup10m"])
-    ap.add_argument("--spp-per-step", type=int, default=64)
+    ap.add_argument("--spp-per-step", type=int, default=0, help="frames (samples per pixel) per step; 0 = the spp BASELINE.json quotes for the workload")
     ap.add_argument("--shard", default="spp", choices=["spp", "tiles"])
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
@@ -266,7 +270,7 @@ def run_b200(args):
     r.synchronize()
     setup_s = time.perf_counter() - t0
 
-    spp = args.spp_per_step
+    spp = args.spp_per_step or CONFIG_SPP[args.workload]
     if world > 1 and args.shard == "spp":
         r.set_shard(rank, world, SHARD_SPLIT_SPP)
         step_frames, scaling = spp * world, "weak"
@@ -328,6 +332,17 @@ def run_b200(args):
                 "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
                 "note": "algorithmic bytes = " + what + "; fetches served by L1/L2 count, so they exceed DRAM traffic "
                         "when the scene is L2-resident (see DESIGN.md section 6)"}
+    # both wavefront kernels side by side (they take about half of a step each, so which one is "dominant" can flip
+    # from run to run): wf_traverse against its fetch bytes, wf_logic against its path-state bytes
+    if "wf_traverse" in kt and "wf_logic" in kt:
+        both = {}
+        for name, tb in (("wf_traverse", bytes_per_ray * my_rays),
+                         ("wf_logic", SHADE_PASS_BYTES * (cal["rays_ext"] - cal["term_miss"]) / max(cal_rays, 1) * my_rays)):
+            ms_k, n_k = kt[name]
+            gbs = tb / max(ms_k * 1e-3, 1e-12) / 1e9
+            both[name] = {"achieved": gbs, "frac": gbs / peak, "launch_ms": ms_k / max(n_k, 1), "launches": n_k,
+                          "share_of_step": ms_k / max(sum(ms), 1e-9)}
+        roofline["per_kernel"] = both
     prof = os.path.join(ROOT, "profiles", "r01_traffic.json")
     if os.path.exists(prof):   # ncu-measured DRAM bytes per ray of this kernel (see the file), scaled to this run's launches
         try:
@@ -412,14 +427,15 @@ def run_b200(args):
             r.set_scene(scenes.default_scene(args.width, args.height))
             r.set_params(max_depth=100)
             r.reset(); r.reset_counters()
-            ms2 = time_steps(r, stream, torch, 2, spp, flush_buf)
+            spp2 = CONFIG_SPP["cornell"]
+            ms2 = time_steps(r, stream, torch, 2, spp2, flush_buf)
             c0 = r.counters()
-            ms2 = time_steps(r, stream, torch, 8, spp, flush_buf)
+            ms2 = time_steps(r, stream, torch, 8, spp2, flush_buf)
             c1 = r.counters()
             line["also"] = {"workload": "cornell (config 2: reference default scene, 1920x1080, max_depth 100)",
                             "value": (c1["rays_ext"] - c0["rays_ext"]) / (sum(ms2) * 1e-3) / 1e6, "unit": UNIT,
                             "total_mrays_s": (c1["rays_ext"] + c1["rays_shadow"] - c0["rays_ext"] - c0["rays_shadow"]) / (sum(ms2) * 1e-3) / 1e6,
-                            "ms_per_frame": sum(ms2) / (8 * spp), "steps": 8, "spp_per_step": spp}
+                            "ms_per_frame": sum(ms2) / (8 * spp2), "steps": 8, "spp_per_step": spp2}
     r.close()
     if world > 1:
         dist.barrier()

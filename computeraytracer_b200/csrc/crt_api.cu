@@ -27,6 +27,7 @@
 struct crt_ctx {
   int device = 0;
   int sm_count = 0;
+  size_t total_mem = 0;
   cudaStream_t stream = nullptr;
   cudaStream_t own_stream = nullptr;
   uint64_t launches = 0;   // hot-path kernel launches since the last crt_reset_counters
@@ -340,11 +341,15 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   // a path lives for at most max_depth+1 extension rays plus one pass for a trailing NEE answer
   const uint64_t worst = (uint64_t)ctx->params.max_depth + 3ull;
   if (worst + 2 > CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_ARG, "max_depth %u is too deep for the wavefront kernel; use CRT_KERNEL_MEGA", ctx->params.max_depth);
-  uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 64u;
-  const uint32_t pool = ctx->params.wf_slots ? ctx->params.wf_slots : (32u << 20);   // measured: 8M -> 114 ms, 16M -> 107 ms, 32M -> 104 ms per 64-spp step of mesh1m
+  // frames per chunk: each chunk ends in a tail of iterations with few live paths (~4 ms on mesh1m), so chunks are as long
+  // as the staging buffer allows (measured: 64 -> 128 -> 256 frames per chunk = 2568 -> 2638 -> 2669 Mrays/s)
+  uint32_t chunk = ctx->params.frames_per_launch ? ctx->params.frames_per_launch : 256u;
+  // path slots in flight, measured per 64-spp step of mesh1m: 8M -> 114 ms, 16M -> 107 ms, 32M -> 104 ms; 64M is another 1-2 %
+  const uint32_t pool = ctx->params.wf_slots ? ctx->params.wf_slots : (64u << 20);
   const size_t n_pixels = ctx->acc_pixels;
-  // guards: staging <= ~8 GB, work items of a chunk < 2^31
-  while (chunk > 1 && ((uint64_t)n_pixels * chunk * 16ull > (8ull << 30) || (uint64_t)n_units * chunk >= (1ull << 31))) chunk--;
+  // guards: staging <= a quarter of the device's memory (45 GB of a B200's 180), work items of a chunk < 2^31
+  const uint64_t stage_cap = std::max<uint64_t>(ctx->total_mem / 4, 1ull << 30);
+  while (chunk > 1 && ((uint64_t)n_pixels * chunk * 16ull > stage_cap || (uint64_t)n_units * chunk >= (1ull << 31))) chunk--;
   const bool split_spp = ctx->shard_mode == CRT_SHARD_SPLIT_SPP && ctx->world > 1;
   // under split-spp a rank renders every world-th frame: size the chunk by the frames this rank renders, not by the
   // frame numbers it spans (8 ranks with 64-frame chunks ran 8 samples per chunk: the pool half empty, 8x the tails)
@@ -466,6 +471,7 @@ int crt_create(int device, crt_ctx** out) {
   if (!ctx) return CRT_ERR_OOM;
   ctx->device = device;
   ctx->sm_count = prop.multiProcessorCount;
+  ctx->total_mem = prop.totalGlobalMem;
   crt_default_params(&ctx->params);
   memset(&ctx->scene, 0, sizeof(ctx->scene));
   memset(&ctx->wf, 0, sizeof(ctx->wf));

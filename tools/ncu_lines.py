@@ -2,7 +2,7 @@
 """Per-source-line summary of an ncu capture: joins `ncu --page source --csv` (SASS rows) with
 `nvdisasm -g` line info of the same cubin, in instruction order.
 
-    python tools/ncu_lines.py REPORT.ncu-rep KERNEL_SUBSTRING [top_n]
+    [NCU_LAUNCH=k] python tools/ncu_lines.py REPORT.ncu-rep KERNEL_SUBSTRING [top_n]
 
 Prints, per source line: warp instructions executed, average active threads, stall samples.
 """
@@ -54,7 +54,8 @@ def main():
             blocks.append(cur)
         elif cur is not None:
             cur["rows"].append(r)
-    blk = [b for b in blocks if ksub in b["name"].replace("(bool)0", "Lb0").replace("(bool)1", "Lb1") or ksub in b["name"]][0]
+    which = int(os.environ.get("NCU_LAUNCH", "0"))   # n-th captured launch of the kernel
+    blk = [b for b in blocks if ksub in b["name"].replace("(bool)0", "Lb0").replace("(bool)1", "Lb1") or ksub in b["name"]][which]
     hdr = blk["rows"][0]
     data = blk["rows"][1:]
     ci = {n: i for i, n in enumerate(hdr)}
