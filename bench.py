@@ -37,7 +37,7 @@ UNIT = "Mrays/s"
 NODE_BYTES = 80   # one 8-wide BVH node fetch (5 x 16 bytes), crt_device.cuh wide_node()
 TRI_BYTES = 48    # one triangle fetch (3 x float4)
 PIXEL_BYTES = 36  # accumulator read 16 + write 16 + framebuffer write 4, once per pixel per launch
-SHADE_PASS_BYTES = 232  # wf_shade per slot: S0..S5 + H read (112) and written (112), queue entries (8)
+SHADE_PASS_BYTES = 232  # wf_logic per extension ray: S0..S5 + H written (112) and read back (112), live-list entry written + read (8)
 QUEUE_RAY_BYTES = 84  # wf_traverse per queued ray: queue entry 4 + origin 16 + direction 16 + exclude word 16 + hit read 16 + hit write 16
 
 
@@ -289,6 +289,9 @@ def run_b200(args):
     r.enable_stats(False)
     cal_rays = cal["rays_ext"] + cal["rays_shadow"]
     bytes_per_ray = (NODE_BYTES * cal["node_visits"] + TRI_BYTES * cal["tri_tests"] + QUEUE_RAY_BYTES * cal["bvh_rays"]) / max(cal_rays, 1)
+    # wf_logic: every extension ray is one pass over its slot's record (written when the ray is made, read when its hit is
+    # consumed); every path stages 16 B of XYZ.  Per (extension + shadow) ray, like bytes_per_ray.
+    logic_bytes_per_ray = (SHADE_PASS_BYTES * cal["rays_ext"] + 16 * cal["paths"]) / max(cal_rays, 1)
 
     # ---- device-timed region (events between the hot-path launches give the per-kernel-class times)
     r.enable_kernel_times(True)
@@ -316,8 +319,8 @@ def run_b200(args):
         total_bytes = bytes_per_ray * my_rays + PIXEL_BYTES * pixels_per_step * k_n
         what = "80 B x BVH nodes visited + 48 B x triangles tested (device counters) + 36 B x pixels per launch"
     elif kernel in ("wf_shade", "wf_logic"):   # path-state traffic: S0..S5 + H read and written once per bounce, queue entries
-        total_bytes = SHADE_PASS_BYTES * (cal["rays_ext"] - cal["term_miss"]) / max(cal_rays, 1) * my_rays
-        what = "232 B of path state (S0..S5, H read + written, queue entries) x surface hits shaded (device counters)"
+        total_bytes = logic_bytes_per_ray * my_rays
+        what = "232 B of path state (S0..S5, H read + written, live-list entry) x extension rays + 16 B of staged XYZ x paths (device counters)"
     else:   # wf_traverse (a BVH scene): the traversal kernel's own fetches
         total_bytes = bytes_per_ray * my_rays
         what = "80 B x BVH nodes visited + 48 B x triangles tested + 84 B x rays queued (device counters of a calibration step)"
@@ -337,7 +340,7 @@ def run_b200(args):
     if "wf_traverse" in kt and "wf_logic" in kt:
         both = {}
         for name, tb in (("wf_traverse", bytes_per_ray * my_rays),
-                         ("wf_logic", SHADE_PASS_BYTES * (cal["rays_ext"] - cal["term_miss"]) / max(cal_rays, 1) * my_rays)):
+                         ("wf_logic", logic_bytes_per_ray * my_rays)):
             ms_k, n_k = kt[name]
             gbs = tb / max(ms_k * 1e-3, 1e-12) / 1e9
             both[name] = {"achieved": gbs, "frac": gbs / peak, "launch_ms": ms_k / max(n_k, 1), "launches": n_k,
