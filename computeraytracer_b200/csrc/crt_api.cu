@@ -270,7 +270,7 @@ int upload_scene(crt_ctx* ctx) {
   }
   const auto t1 = std::chrono::steady_clock::now();
   ctx->stats[0] = n_prims; ctx->stats[1] = s.n_lin; ctx->stats[2] = s.n_tri; ctx->stats[3] = s.n_nodes;
-  ctx->stats[4] = (uint64_t)s.n_nodes * 80; ctx->stats[5] = (uint64_t)s.n_tri * 48;
+  ctx->stats[4] = (uint64_t)s.n_nodes * 16 * CRT_NODE_STRIDE; ctx->stats[5] = (uint64_t)s.n_tri * 48;
   ctx->stats[6] = (uint64_t)std::chrono::duration_cast<std::chrono::microseconds>(t1 - t0).count();
   ctx->stats[7] = bvh.max_depth;
   ctx->scene_dirty = false;

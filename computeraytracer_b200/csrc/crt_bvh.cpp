@@ -238,7 +238,7 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
   std::vector<uint32_t> wide_src{0};      // wide node -> BVH2 node it was collapsed from
   std::vector<uint32_t> wide_depth{1};
   out.tri_src.reserve(n);
-  out.nodes.reserve((n / 4 + 16) * 20);
+  out.nodes.reserve((n / 4 + 16) * 4 * CRT_NODE_STRIDE);
   for (size_t k = 0; k < wide_src.size(); k++) {
     const BNode& top = pool[wide_src[k]];
     uint32_t ch[8]; int nc = 0;
@@ -316,6 +316,7 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
     std::memcpy(&w[8], qlo[0], 8); std::memcpy(&w[10], qlo[1], 8); std::memcpy(&w[12], qlo[2], 8);
     std::memcpy(&w[14], qhi[0], 8); std::memcpy(&w[16], qhi[1], 8); std::memcpy(&w[18], qhi[2], 8);
     out.nodes.insert(out.nodes.end(), w, w + 20);
+    for (int pad_w = 20; pad_w < 4 * CRT_NODE_STRIDE; pad_w++) out.nodes.push_back(0u);
     out.max_depth = std::max(out.max_depth, wide_depth[k]);
   }
   out.n_nodes = (uint32_t)wide_src.size();

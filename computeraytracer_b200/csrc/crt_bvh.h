@@ -1,5 +1,8 @@
 // crt_bvh.h -- host-side BVH construction for the scene-upload module.
 #pragma once
+#ifndef CRT_NODE_STRIDE
+#define CRT_NODE_STRIDE 5   // 16-byte words between consecutive Wide8 nodes (5 = packed; 6 = 96-byte stride, tuning)
+#endif
 #include <stdint.h>
 #include <vector>
 

@@ -148,6 +148,8 @@ struct Hit {
 };
 
 // ray_intersection for one linear-list entry, CS:520-632, sequential semantics (called in index order).
+// (The early exits stay: evaluating the patch test without them -- same tests, predicated -- made wf_logic 26 % slower;
+// whole warps leave at the exits often enough.)
 __device__ __forceinline__ void test_lin(const LinPrim& p, uint32_t slot, V3 o, V3 d, uint32_t exclude, float t_min, Hit& h) {
   uint32_t index = __float_as_uint(p.A.w);
   if (exclude == index) return;                      // CS:529 / CS:588
@@ -216,6 +218,9 @@ __device__ __forceinline__ bool test_tri(float4 T0, float4 T1, float4 T2, V3 o, 
 // with (tnear <= tfar), tfar clamped to the best t so far, never drops a primitive the linear scan would accept
 // (DESIGN.md "Conservative culling"); equal-t ties go to the higher primitive index, which is what the reference's in-order
 // scan with `t > t_max` rejection yields.
+#ifndef CRT_NODE_STRIDE
+#define CRT_NODE_STRIDE 5
+#endif
 #define CRT_WIDE_HITS 0xFF000000u   // group word: bits 24..31 = inner children still to visit (priority order), 0..7 = imask
 
 struct WideRay {     // per-ray constants of the traversal
@@ -308,11 +313,11 @@ __device__ __forceinline__ void wide_node_eval(const uint4 w0, const uint4 w1, c
 template <bool STATS>
 __device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint32_t node, const WideRay& r, uint32_t one, float t_min,
                                           float t_max, uint2& G, uint2& T, Stats& st) {
-  const uint4 w0 = __ldg(&nodes[5 * node + 0]);
-  const uint4 w1 = __ldg(&nodes[5 * node + 1]);
-  const uint4 w2 = __ldg(&nodes[5 * node + 2]);
-  const uint4 w3 = __ldg(&nodes[5 * node + 3]);
-  const uint4 w4 = __ldg(&nodes[5 * node + 4]);
+  const uint4 w0 = __ldg(&nodes[CRT_NODE_STRIDE * node + 0]);
+  const uint4 w1 = __ldg(&nodes[CRT_NODE_STRIDE * node + 1]);
+  const uint4 w2 = __ldg(&nodes[CRT_NODE_STRIDE * node + 2]);
+  const uint4 w3 = __ldg(&nodes[CRT_NODE_STRIDE * node + 3]);
+  const uint4 w4 = __ldg(&nodes[CRT_NODE_STRIDE * node + 4]);
   wide_node_eval<STATS>(w0, w1, w2, w3, w4, r, one, t_min, t_max, G, T, st);
 }
 

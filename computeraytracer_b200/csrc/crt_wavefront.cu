@@ -26,6 +26,9 @@
 #ifndef WF_BLOCK
 #define WF_BLOCK 256
 #endif
+#ifndef WF_LOGIC_BLOCK
+#define WF_LOGIC_BLOCK WF_BLOCK
+#endif
 
 // One slot's record: WF_REC_WORDS 16-byte words, contiguous, so that every 32-byte DRAM sector a kernel touches is used
 // in full (the first version kept one array per word: each access pulled a half-used sector from a different DRAM page,
@@ -478,7 +481,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
 // different phases (ncu: ~17 of 32 active), but these kernels wait on memory and on dependent arithmetic rather than on
 // issue slots, and the fused form makes one pass over a slot's record per bounce instead of up to two.
 template <bool STATS>
-__global__ void __launch_bounds__(WF_BLOCK) wf_logic(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
+__global__ void __launch_bounds__(WF_LOGIC_BLOCK) wf_logic(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
                                                      unsigned long long* __restrict__ counters) {
   extern __shared__ float s_tables[];
   const float *spectra, *cie;
@@ -757,7 +760,7 @@ cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* sh
   if ((e = cudaFuncSetAttribute(wf_logic<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
   if ((e = cudaFuncSetAttribute(wf_shade<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
   if ((e = cudaFuncSetAttribute(wf_regen<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
-  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<S>, WF_LOGIC_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(regen_blocks_per_sm, wf_regen<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(trav_blocks_per_sm, wf_traverse<S, true>, WF_BLOCK, 0);
@@ -768,8 +771,8 @@ cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* sh
 
 cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s) {
-  if (stats) wf_logic<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
-  else wf_logic<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  if (stats) wf_logic<true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  else wf_logic<false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, ck, it, counters);
   return cudaGetLastError();
 }
 

@@ -72,9 +72,12 @@ typedef struct crt_params {
   float    t_min;       /* create_intersection_context, CS:720 (0.001)                    */
   float    exposure;    /* tone_map argument, CS:112 (2.2)                                */
   uint32_t kernel;      /* enum crt_kernel; AUTO picks from the scene         */
-  uint32_t frames_per_launch; /* 0 = library default; samples one lane integrates in-register */
+  uint32_t frames_per_launch; /* frames per launch (megakernel: samples a lane integrates in registers) or per
+                                 wavefront chunk; 0 = library default (wavefront: up to 256, bounded by the
+                                 staging buffer); results never depend on it                              */
   uint32_t flags;       /* CRT_FLAG_* bits (instrumentation; results never depend on them)     */
-  uint32_t wf_slots;    /* wavefront kernel: path slots in flight (0 = library default)        */
+  uint32_t wf_slots;    /* wavefront kernel: path slots in flight (0 = library default, 64 Mi);
+                           results never depend on it                                           */
   uint32_t reserved[4];
 } crt_params;
 

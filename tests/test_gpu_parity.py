@@ -363,3 +363,16 @@ def test_soup_200k_radiance_parity_vs_oracle_bvh(gpu, oracle):
     assert_radiance(acc, acc_c, 2)
     assert np.array_equal(fb, fb_c)
     assert cg == (int(cc[0]), int(cc[1]), int(cc[2]))
+
+
+@pytest.mark.parametrize("wf_slots,chunk", [(1024, 0), (4096, 2), (0, 3), (100_000, 7)])
+def test_wavefront_pool_and_chunk_size_never_change_results(gpu, oracle, wf_slots, chunk):
+    """The path-slot pool (how many paths are in flight, which slot runs which pixel-sample) and the chunk length (how
+    many frames share a wavefront) are scheduling only: accumulator, framebuffer and counters stay those of the oracle."""
+    ps = scenes.mesh_scene(96, 64, n_lon=64, n_lat=32)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    acc, fb, cg = _render(gpu, 7, kernel=2, max_depth=8, wf_slots=wf_slots, frames_per_launch=chunk)
+    acc_c, fb_c, cc = oracle.scene(ps, default_params(max_depth=8)).render(7)
+    assert_radiance(acc, acc_c, 7)
+    assert np.array_equal(fb, fb_c)
+    assert cg == (int(cc[0]), int(cc[1]), int(cc[2]))
