@@ -58,6 +58,7 @@ def parse_args():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--frames-per-launch", type=int, default=0)
     ap.add_argument("--pool", type=int, default=0, help="wavefront path slots in flight (0 = library default)")
+    ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront"], help="force one form of the hot path (default: chosen from the scene)")
     ap.add_argument("--wf-split", action="store_true", help="wavefront: wf_shade + wf_regen kernels instead of the single wf_logic")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -261,8 +262,9 @@ def run_b200(args):
     t0 = time.perf_counter()
     r.set_scene(ps)
     p = r.set_params(max_depth=max_depth, frames_per_launch=args.frames_per_launch)
-    if args.pool or args.wf_split:
+    if args.pool or args.wf_split or args.kernel != "auto":
         p.wf_slots = args.pool
+        p.kernel = {"auto": 0, "mega": 1, "wavefront": 2}[args.kernel]
         if args.wf_split:
             p.flags |= 4   # CRT_FLAG_WF_SPLIT
         r.set_params(p)

@@ -598,10 +598,14 @@ int crt_dispatch_frames(crt_ctx* ctx, uint32_t n) {
   if (ctx->shard_mode == CRT_SHARD_TILES && ctx->world > 1)
     n_tiles = (n_tiles > ctx->rank) ? (n_tiles - ctx->rank + ctx->world - 1) / ctx->world : 0;
   const uint32_t n_units = n_tiles * 32u;
-  // AUTO: the wavefront form when there is a BVH (ncu: the megakernel runs 4.75 of 32 lanes there), the
-  // megakernel for linear-list-only scenes (all lanes share the same primitive loop)
+  // AUTO: the wavefront form when there is a BVH (ncu: the megakernel runs 4.75 of 32 lanes there) and, for linear-list
+  // scenes, whenever the dispatch has two frames or more.  Measured on the reference's default scene at 1080p
+  // (profiles/r01r_auto_threshold.txt), ms per dispatch of 1 / 2 / 4 / 64 frames: megakernel 2.2 / 4.4 / 8.3 / 125,
+  // wavefront 2.8 / 3.8 / 5.6 / 64 -- the wavefront pays ~2 ms per dispatch for the thin iterations of the paths that loop
+  // to max_depth inside the glass sphere and half the megakernel's time per frame after that.  Both forms give the same bits.
   uint32_t kernel = ctx->params.kernel;
-  if (kernel == CRT_KERNEL_AUTO) kernel = (s.n_tri > 0 && ctx->params.max_depth <= 1000) ? CRT_KERNEL_WAVEFRONT : CRT_KERNEL_MEGA;
+  if (kernel == CRT_KERNEL_AUTO)
+    kernel = (ctx->params.max_depth <= 1000 && (s.n_tri > 0 || n >= 2)) ? CRT_KERNEL_WAVEFRONT : CRT_KERNEL_MEGA;
   // a light that is itself a triangle needs closest-hit shadow rays: only the megakernel carries that path
   if (s.shadow_closest) kernel = CRT_KERNEL_MEGA;
   CU(cudaEventRecord(ctx->ev_start, ctx->stream));
