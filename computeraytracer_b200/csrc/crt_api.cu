@@ -53,7 +53,8 @@ struct crt_ctx {
   float* d_spectra = nullptr; float* d_cie = nullptr;
   void* d_prims_raw = nullptr;   // binding 8 as uploaded
   LinPrim* d_lin = nullptr; LightRec* d_lights = nullptr;
-  float4* d_tri = nullptr; uint4* d_nodes = nullptr;
+  float4* d_tri = nullptr; uint4* d_nodes = nullptr;   // one allocation: nodes, then triangles (d_tri points into it)
+  size_t scene_bytes = 0;
   uint32_t* d_work = nullptr;
   unsigned long long* d_counters = nullptr;
   DevScene scene;
@@ -74,8 +75,8 @@ struct crt_ctx {
   // CRT_FLAG_KERNEL_TIMES: events recorded between consecutive hot-path launches
   std::vector<cudaEvent_t> ev_free;
   std::vector<std::pair<cudaEvent_t, int>> ev_seq;   // (event, class of the kernel launched right after it; -1 = end of a run)
-  double k_ms[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0, 0, 0};
-  uint64_t k_launches[CRT_NUM_KERNEL_CLASSES] = {0, 0, 0, 0, 0, 0};
+  double k_ms[CRT_NUM_KERNEL_CLASSES] = {};
+  uint64_t k_launches[CRT_NUM_KERNEL_CLASSES] = {};
 };
 
 namespace {
@@ -216,7 +217,7 @@ int upload_scene(crt_ctx* ctx) {
   crt::build_bvh(prims, tri_pos, threads, bvh);
   if (bvh.max_depth + 2 > CRT_BVH_STACK) return fail(ctx, CRT_ERR_SIZE, "BVH depth %u exceeds the traversal stack", bvh.max_depth);
 
-  dfree(ctx->d_prims_raw); dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_tri); dfree(ctx->d_nodes);
+  dfree(ctx->d_prims_raw); dfree(ctx->d_lin); dfree(ctx->d_lights); ctx->d_tri = nullptr; dfree(ctx->d_nodes); ctx->scene_bytes = 0;
   DevScene& s = ctx->scene;
   s.n_lin = (uint32_t)lin_pos.size(); s.n_tri = (uint32_t)tri_pos.size(); s.n_nodes = bvh.n_nodes; s.n_lights = (uint32_t)n_lights;
   s.lin_g = nullptr; s.tri = nullptr; s.nodes = nullptr; s.lights_g = nullptr;
@@ -239,8 +240,11 @@ int upload_scene(crt_ctx* ctx) {
     s.lin_g = ctx->d_lin;
   }
   if (s.n_tri) {
-    CU(cudaMalloc(&ctx->d_tri, (size_t)s.n_tri * 48));
-    CU(cudaMalloc(&ctx->d_nodes, bvh.nodes.size() * 4));
+    // one allocation, nodes first: an L2 access-policy window (below) is a single address range
+    const size_t node_bytes = (bvh.nodes.size() * 4 + 255) & ~(size_t)255, tri_bytes = (size_t)s.n_tri * 48;
+    CU(cudaMalloc(&ctx->d_nodes, node_bytes + tri_bytes));
+    ctx->d_tri = (float4*)((uint8_t*)ctx->d_nodes + node_bytes);
+    ctx->scene_bytes = node_bytes + tri_bytes;
     CU(cudaMemcpyAsync(d_src, bvh.tri_src.data(), bvh.tri_src.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     CU(crt::launch_repack_tri(ctx->d_prims_raw, d_src, s.n_tri, ctx->d_tri, ctx->stream));
     CU(cudaMemcpyAsync(ctx->d_nodes, bvh.nodes.data(), bvh.nodes.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -268,6 +272,32 @@ int upload_scene(crt_ctx* ctx) {
     }
     if (s.shadow_closest) break;
   }
+  // CRT_L2_PERSIST=1 (tuning): keep nodes and triangles in the persisting part of L2 while the wavefront kernels stream
+  // the slot records through the rest.  The window covers the nodes first; if the scene is larger than the persisting
+  // carve-out, hitRatio scales the share of lines that are kept.
+  {
+    const char* e = getenv("CRT_L2_PERSIST");
+    cudaStreamAttrValue attr;
+    memset(&attr, 0, sizeof(attr));
+    if (e && atoi(e) > 0 && ctx->scene_bytes) {
+      cudaDeviceProp prop;
+      int dev = 0;
+      CU(cudaGetDevice(&dev));
+      CU(cudaGetDeviceProperties(&prop, dev));
+      const size_t carve = std::min<size_t>((size_t)prop.persistingL2CacheMaxSize, ctx->scene_bytes);
+      const size_t win = std::min<size_t>((size_t)prop.accessPolicyMaxWindowSize, atoi(e) == 2 ? (size_t)s.n_nodes * 16 * CRT_NODE_STRIDE : ctx->scene_bytes);
+      if (carve && win) {
+        CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
+        attr.accessPolicyWindow.base_ptr = ctx->d_nodes;
+        attr.accessPolicyWindow.num_bytes = win;
+        attr.accessPolicyWindow.hitRatio = win <= carve ? 1.0f : (float)((double)carve / (double)win);
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+        fprintf(stderr, "[crt] L2 persisting window: %zu bytes, carve-out %zu of max %d, hit ratio %.2f\n", win, carve, prop.persistingL2CacheMaxSize, attr.accessPolicyWindow.hitRatio);
+      }
+    }
+    CU(cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+  }
   const auto t1 = std::chrono::steady_clock::now();
   ctx->stats[0] = n_prims; ctx->stats[1] = s.n_lin; ctx->stats[2] = s.n_tri; ctx->stats[3] = s.n_nodes;
   ctx->stats[4] = (uint64_t)s.n_nodes * 16 * CRT_NODE_STRIDE; ctx->stats[5] = (uint64_t)s.n_tri * 48;
@@ -291,6 +321,15 @@ int prepare(crt_ctx* ctx) {
   return CRT_OK;
 }
 
+#ifndef CRT_WF_LIVE_BVH
+#define CRT_WF_LIVE_BVH 0      // live mode for scenes with triangles
+#endif
+#ifndef CRT_WF_LIVE_LINEAR
+#define CRT_WF_LIVE_LINEAR 1   // live mode for linear-list scenes (reference default scene 1080p x 64 frames: 64.8 -> 55.0 ms)
+#endif
+#ifndef CRT_WF_STATIC_EIGHTHS
+#define CRT_WF_STATIC_EIGHTHS 0
+#endif
 constexpr size_t kWfCounterBytes = (size_t)(CRT_WF_MAX_ITERS + 2) * sizeof(WfIter) + 64;   // iteration records + the work counter
 
 int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
@@ -298,7 +337,8 @@ int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
   if (ctx->wf_mem) { cudaFree(ctx->wf_mem); ctx->wf_mem = nullptr; }
   // one record per slot; shade and finish queues of two iterations, the regen queue, the BVH queue (2 entries per slot)
   const size_t slow_bytes = (size_t)(1 + 3 * CRT_WF_SLOW_RAYS) * 16;
-  const size_t total = (size_t)(CRT_WF_REC_WORDS * 16 + 7 * 4) * n_slots + kWfCounterBytes + 256 + slow_bytes;
+  const size_t cls_bytes = ((size_t)n_slots + 255) & ~(size_t)255;
+  const size_t total = (size_t)(CRT_WF_REC_WORDS * 16 + 7 * 4) * n_slots + kWfCounterBytes + 256 + slow_bytes + cls_bytes;
   CU(cudaMalloc(&ctx->wf_mem, total));
   uint8_t* p = (uint8_t*)ctx->wf_mem;
   WfState& w = ctx->wf;
@@ -312,7 +352,8 @@ int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
   w.shadow_list = (uint32_t*)p; p += 4 * (size_t)n_slots;
   w.iter = (WfIter*)p; p += (size_t)(CRT_WF_MAX_ITERS + 2) * sizeof(WfIter);
   w.work = (uint32_t*)p; p += 256;
-  w.slow = (float4*)p;
+  w.slow = (float4*)p; p += slow_bytes;
+  w.cls = (uint8_t*)p;
   CU(cudaMemset(w.slow, 0, slow_bytes));
   {
     const char* e = getenv("CRT_SLOW_RAY_NODES");   // diagnostics: log rays that visit at least this many nodes (stats mode)
@@ -354,6 +395,14 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   // under split-spp a rank renders every world-th frame: size the chunk by the frames this rank renders, not by the
   // frame numbers it spans (8 ranks with 64-frame chunks ran 8 samples per chunk: the pool half empty, 8x the tails)
   if (split_spp) chunk = (uint32_t)std::min<uint64_t>((uint64_t)chunk * ctx->world, 1u << 20);
+  // how wf_logic's live slots reach the next iteration (crt_wavefront.cu, wf_emit): 0 one list, 1 routed lists, 2 class
+  // bytes + wf_partition.  In 1 and 2 wf_logic runs over the finish list and then the bounce list, so the lanes of a warp
+  // are in one phase.
+  uint32_t live_mode = s.n_tri ? CRT_WF_LIVE_BVH : CRT_WF_LIVE_LINEAR;
+  if (const char* e = getenv("CRT_WF_ROUTED")) live_mode = (uint32_t)atoi(e) % 3u;   // tuning override
+  if (split) live_mode = 0;
+  uint32_t static_eighths = CRT_WF_STATIC_EIGHTHS;
+  if (const char* e = getenv("CRT_WF_STATIC")) static_eighths = std::min<uint32_t>((uint32_t)strtoul(e, nullptr, 10), 8u);   // tuning override
   uint32_t left = n;
   while (left) {
     const uint32_t k = left < chunk ? left : chunk;
@@ -376,6 +425,8 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       chunk = std::max(1u, k / 2);
       continue;
     }
+    // static share of the work items (eighths of the whole rounds of the pool; wf_logic only): see wf_logic's work loop
+    ck.n_static = split ? 0u : (uint32_t)((total_work / ck.n_slots) * static_eighths / 8u) * ck.n_slots;
     const size_t stage_bytes = (size_t)std::max(1u, ck.n_samples) * n_pixels * 16;
     if (stage_bytes > ctx->wf_stage_bytes) {
       if (ctx->wf_stage) { cudaFree(ctx->wf_stage); ctx->wf_stage = nullptr; ctx->wf_stage_bytes = 0; }
@@ -392,7 +443,7 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       for (;;) {
         if (!split) {
           CU(mark(ctx, CRT_KC_WF_LOGIC));
-          CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, grid_l, smem, it, ctx->d_counters, ctx->stream));
+          CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, live_mode, grid_l, smem, it, ctx->d_counters, ctx->stream));
           ctx->launches++;
         } else {
           if (it) {
@@ -406,7 +457,12 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
         }
         if (s.n_tri) {
           CU(mark(ctx, CRT_KC_WF_TRAVERSE));
-          CU(crt::launch_wf_traverse(s, ctx->wf, stats, split, grid_t, it, ctx->d_counters, ctx->stream));
+          CU(crt::launch_wf_traverse(s, ctx->wf, stats, split || live_mode == 1, live_mode == 2, grid_t, it, ctx->d_counters, ctx->stream));
+          ctx->launches++;
+        }
+        if (live_mode == 2) {
+          CU(mark(ctx, CRT_KC_WF_PARTITION));
+          CU(crt::launch_wf_partition(ctx->wf, ck.n_slots, ctx->sm_count * 8, it, ctx->stream));
           ctx->launches++;
         }
         it++;
@@ -492,7 +548,7 @@ void crt_destroy(crt_ctx* ctx) {
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   dfree(ctx->d_acc); dfree(ctx->d_fb); dfree(ctx->d_tea); dfree(ctx->d_spectra); dfree(ctx->d_cie); dfree(ctx->d_prims_raw);
-  dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_tri); dfree(ctx->d_nodes); dfree(ctx->d_work); dfree(ctx->d_counters);
+  dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_nodes); dfree(ctx->d_work); dfree(ctx->d_counters);
   if (ctx->wf_mem) cudaFree(ctx->wf_mem);
   if (ctx->wf_stage) cudaFree(ctx->wf_stage);
   if (ctx->wf_host_count) cudaFreeHost(ctx->wf_host_count);

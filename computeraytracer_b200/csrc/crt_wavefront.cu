@@ -29,6 +29,12 @@
 #ifndef WF_LOGIC_BLOCK
 #define WF_LOGIC_BLOCK WF_BLOCK
 #endif
+#ifndef WF_LOGIC_MIN_BLOCKS
+#define WF_LOGIC_MIN_BLOCKS 3   // 3 x 256 threads per SM = 85 registers at most (ptxas picks 106 without the bound)
+#endif
+#ifndef WF_STATIC_WORK
+#define WF_STATIC_WORK 1   // wf_logic honours WfChunk::n_static (0 = every work item through the global counter)
+#endif
 
 // One slot's record: WF_REC_WORDS 16-byte words, contiguous, so that every 32-byte DRAM sector a kernel touches is used
 // in full (the first version kept one array per word: each access pulled a half-used sector from a different DRAM page,
@@ -41,9 +47,17 @@ enum {
   WF_R_S2 = 6, WF_R_S3 = 7,   // sector D: accumulated radiance, beta
   WF_R_S4 = 8                 // sector E: RNG state (+ 16 bytes spare)
 };
-__device__ __forceinline__ float4& wf_f4(const WfState& w, uint32_t slot, int word) { return w.rec[(size_t)slot * WF_REC_WORDS + word]; }
-__device__ __forceinline__ uint4& wf_u4(const WfState& w, uint32_t slot, int word) {
-  return reinterpret_cast<uint4*>(w.rec)[(size_t)slot * WF_REC_WORDS + word];
+// Record accessors.  With CRT_L2_REC the records -- a multi-gigabyte stream that every iteration reads and rewrites once --
+// go through L2 with an evict-first policy, so that they do not push the scene (nodes, triangles) out of L2.
+__device__ __forceinline__ float4* rec_ptr(const WfState& w, uint32_t slot, int word) { return &w.rec[(size_t)slot * WF_REC_WORDS + word]; }
+__device__ __forceinline__ float4 rec_ld(const WfState& w, uint32_t slot, int word) { return ld_stream(rec_ptr(w, slot, word)); }
+__device__ __forceinline__ uint4 rec_ldu(const WfState& w, uint32_t slot, int word) {
+  const float4 v = rec_ld(w, slot, word);
+  return make_uint4(__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
+}
+__device__ __forceinline__ void rec_st(const WfState& w, uint32_t slot, int word, float4 v) { st_stream(rec_ptr(w, slot, word), v); }
+__device__ __forceinline__ void rec_stu(const WfState& w, uint32_t slot, int word, uint4 v) {
+  rec_st(w, slot, word, make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w)));
 }
 #define WF_FLAG_SPECULAR 1u
 #define WF_FLAG_TRANSMISSION 2u
@@ -61,14 +75,14 @@ __device__ __forceinline__ bool unit_pixel(const DevScene& sc, uint32_t unit, ui
 }
 
 __device__ __forceinline__ void wf_load(const WfState& w, uint32_t slot, PathState& ps, Rng& rng, uint32_t& wid, uint32_t& flags) {
-  const float4 a = wf_f4(w, slot, WF_R_S0), b = wf_f4(w, slot, WF_R_S1);
+  const float4 a = rec_ld(w, slot, WF_R_S0), b = rec_ld(w, slot, WF_R_S1);
   ps.o = v3(a); ps.pdf = a.w;
   ps.d = v3(b); ps.etaScale = b.w;
-  ps.L = wf_f4(w, slot, WF_R_S2);
-  ps.beta = wf_f4(w, slot, WF_R_S3);
-  const uint4 r = wf_u4(w, slot, WF_R_S4);
+  ps.L = rec_ld(w, slot, WF_R_S2);
+  ps.beta = rec_ld(w, slot, WF_R_S3);
+  const uint4 r = rec_ldu(w, slot, WF_R_S4);
   rng.x = r.x; rng.y = r.y; rng.z = r.z; rng.w = r.w;
-  const uint4 m = wf_u4(w, slot, WF_R_S5);
+  const uint4 m = rec_ldu(w, slot, WF_R_S5);
   ps.exclude = m.x;
   ps.depth = m.y & 0xFFFFu;
   flags = (m.y >> 16) & 0xFu;
@@ -80,13 +94,13 @@ __device__ __forceinline__ void wf_load(const WfState& w, uint32_t slot, PathSta
 
 __device__ __forceinline__ void wf_store(const WfState& w, uint32_t slot, const PathState& ps, const Rng& rng, uint32_t wid, uint32_t flags,
                                          uint32_t light_prim) {
-  wf_f4(w, slot, WF_R_S0) = make_float4(ps.o.x, ps.o.y, ps.o.z, ps.pdf);
-  wf_f4(w, slot, WF_R_S1) = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.etaScale);
-  wf_f4(w, slot, WF_R_S2) = ps.L;
-  wf_f4(w, slot, WF_R_S3) = ps.beta;
-  wf_u4(w, slot, WF_R_S4) = make_uint4(rng.x, rng.y, rng.z, rng.w);
+  rec_st(w, slot, WF_R_S0, make_float4(ps.o.x, ps.o.y, ps.o.z, ps.pdf));
+  rec_st(w, slot, WF_R_S1, make_float4(ps.d.x, ps.d.y, ps.d.z, ps.etaScale));
+  rec_st(w, slot, WF_R_S2, ps.L);
+  rec_st(w, slot, WF_R_S3, ps.beta);
+  rec_stu(w, slot, WF_R_S4, make_uint4(rng.x, rng.y, rng.z, rng.w));
   const uint32_t fl = (flags & (WF_FLAG_PENDING | WF_FLAG_DEAD)) | (ps.specular ? WF_FLAG_SPECULAR : 0u) | (ps.in_transmission ? WF_FLAG_TRANSMISSION : 0u);
-  wf_u4(w, slot, WF_R_S5) = make_uint4(ps.exclude, (ps.depth & 0xFFFFu) | (fl << 16) | (ps.lam0 << 20), light_prim, wid);
+  rec_stu(w, slot, WF_R_S5, make_uint4(ps.exclude, (ps.depth & 0xFFFFu) | (fl << 16) | (ps.lam0 << 20), light_prim, wid));
 }
 
 // Appending to a global queue costs one atomic per warp, in two steps so that several queues can be served with the
@@ -254,13 +268,13 @@ __device__ __forceinline__ void wf_finish(const DevScene& sc, const WfChunk& ck,
   const uint32_t j = wid / ck.n_units;
   uint32_t px, py;
   unit_pixel(sc, wid - j * ck.n_units, px, py);
-  ck.stage[(size_t)j * ck.n_pixels + (px + py * sc.W)] = make_float4(xyz.x, xyz.y, xyz.z, 0.0f);   // CS:107
+  st_stream(&ck.stage[(size_t)j * ck.n_pixels + (px + py * sc.W)], make_float4(xyz.x, xyz.y, xyz.z, 0.0f));   // CS:107
 }
 
 // the pending NEE contribution of a slot, as the reference would have added it (CS:187 with CS:400 or CS:407)
 __device__ __forceinline__ void wf_add_pending(const WfState& w, uint32_t slot, float4& L) {
-  const bool occluded = wf_f4(w, slot, WF_R_S6).w < 0.0f;   // wf_traverse marks an occluded segment by a negative length
-  float4 c = wf_f4(w, slot, WF_R_S7);
+  const bool occluded = ld_stream1(reinterpret_cast<const float*>(rec_ptr(w, slot, WF_R_S6)) + 3) < 0.0f;   // wf_traverse marks an occluded segment by a negative length
+  float4 c = rec_ld(w, slot, WF_R_S7);
   if (occluded) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407: Le = 0, the sum still happens
   L.x += c.x; L.y += c.y; L.z += c.z; L.w += c.w;
 }
@@ -305,26 +319,37 @@ __device__ __forceinline__ void wf_counts_flush(const LogicCounts& lc, const Sta
 // bounds it is queued for the BVH (wf_traverse then routes the slot by the final hit), otherwise the hit is final and the
 // slot goes straight to the next iteration's shade queue (surface hit) or finish queue (miss).  A slot that only waits for
 // an NEE answer goes to the finish queue.  Called by whole warps.
-template <bool STATS, bool SPLIT>
-__device__ __forceinline__ void wf_emit(const DevScene& sc, const WfState& w, uint32_t it, bool alive, bool has_ext, uint32_t slot,
+// `mode` says how the live slots reach the next iteration: WF_LIVE_LIST = one live list in processing order (bounce[]);
+// WF_LIVE_ROUTED = pushed here (and by wf_traverse) to the bounce or finish list by the slot's final hit; WF_LIVE_CLASS =
+// no list at all: the slot's class byte is written (w.cls: 0 bounce, 1 finish, 2 retired; wf_traverse corrects it when a
+// triangle turns a miss into a hit) and wf_partition builds both lists in slot order after the traversal.
+enum { WF_LIVE_LIST = 0, WF_LIVE_ROUTED = 1, WF_LIVE_CLASS = 2 };
+template <bool STATS>
+__device__ __forceinline__ void wf_emit(const DevScene& sc, const WfState& w, uint32_t it, uint32_t mode, bool valid, bool alive, bool has_ext, uint32_t slot,
                                         const PathState& ps, const Rng& rng, uint32_t wid, uint32_t flags, const NeeQuery& nee,
                                         Stats& st, LogicCounts& lc) {
-  bool want_bvh = false, to_bounce = false;
+  bool want_bvh = false, to_bounce = false, lin_hit = false;
   if (has_ext) {
     const Hit h = scan_linear<STATS>(sc, ps.o, ps.d, ps.exclude, st);
     lc.n_ext++;
     want_bvh = hits_root_box(sc, ps.o, ps.d, h.t);
-    to_bounce = !want_bvh && h.idx != CRT_MAX_U32;
-    wf_f4(w, slot, WF_R_H) = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f);
+    lin_hit = h.idx != CRT_MAX_U32;
+    to_bounce = !want_bvh && lin_hit;
+    rec_st(w, slot, WF_R_H, make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f));
   }
-  if (!SPLIT) to_bounce = alive;   // single-kernel form: one live list
-  const bool to_finish = alive && !want_bvh && !to_bounce;
+  if (mode == WF_LIVE_LIST) to_bounce = alive;   // unrouted single-kernel form: one live list
+  bool to_finish = alive && !want_bvh && !to_bounce;
   const bool shadow = alive && nee.pending;
+  if (mode == WF_LIVE_CLASS) {
+    // class of the slot's next pass as far as the linear list knows it: a hit there stays a hit whatever the BVH adds
+    if (valid) w.cls[slot] = !alive ? (uint8_t)2 : (lin_hit ? (uint8_t)0 : (uint8_t)1);
+    to_bounce = false; to_finish = false;
+  }
   if (alive) {
     wf_store(w, slot, ps, rng, wid, flags, nee.light_prim);
     if (shadow) {
-      wf_f4(w, slot, WF_R_S6) = make_float4(nee.d.x, nee.d.y, nee.d.z, nee.t);
-      wf_f4(w, slot, WF_R_S7) = nee.c;
+      rec_st(w, slot, WF_R_S6, make_float4(nee.d.x, nee.d.y, nee.d.z, nee.t));
+      rec_st(w, slot, WF_R_S7, nee.c);
     }
   }
   const uint32_t nx = (it + 1u) & 1u;
@@ -388,7 +413,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
       slot = cur[i];
       wf_load(w, slot, ps, rng, wid, flags);
       if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // before anything else is added to L
-      const float4 hv = wf_f4(w, slot, WF_R_H);
+      const float4 hv = rec_ld(w, slot, WF_R_H);
       Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
       uint32_t term = 0;
       const int r = wf_bounce<STATS>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
@@ -400,7 +425,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
       if (ended) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
     }
     const PushTicket tr = wf_reserve(ended, &w.iter[it].n_regen);   // in flight while wf_emit scans the linear list
-    wf_emit<STATS, true>(sc, w, it, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
+    wf_emit<STATS>(sc, w, it, WF_LIVE_ROUTED, true, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
     wf_commit(tr, ended, slot, w.regen);
   }
   wf_counts_flush<STATS>(lc, st, counters);
@@ -438,9 +463,9 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
         slot = i;
       } else if (i < n_fin) {
         slot = fin[i];
-        const uint4 m = wf_u4(w, slot, WF_R_S5);
+        const uint4 m = rec_ldu(w, slot, WF_R_S5);
         const uint32_t flags = (m.y >> 16) & 0xFu;
-        float4 L = wf_f4(w, slot, WF_R_S2);
+        float4 L = rec_ld(w, slot, WF_R_S2);
         if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, L);
         wf_finish(sc, ck, cie, L, m.y >> 20, m.w);
         if (STATS && !(flags & WF_FLAG_DEAD)) { lc.term_cnt[0]++; lc.depth_sum += m.y & 0xFFFFu; }
@@ -471,7 +496,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
       mask = __ballot_sync(0xffffffffu, need);   // lanes that drew a unit outside the image fetch again
       if (mask != 0u && lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
     }
-    wf_emit<STATS, true>(sc, w, it, alive, alive, slot, ps, rng, wid, 0u, nee, st, lc);
+    wf_emit<STATS>(sc, w, it, WF_LIVE_ROUTED, true, alive, alive, slot, ps, rng, wid, 0u, nee, st, lc);
   }
   wf_counts_flush<STATS>(lc, st, counters);
 }
@@ -481,13 +506,21 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
 // different phases (ncu: ~17 of 32 active), but these kernels wait on memory and on dependent arithmetic rather than on
 // issue slots, and the fused form makes one pass over a slot's record per bounce instead of up to two.
 template <bool STATS>
-__global__ void __launch_bounds__(WF_LOGIC_BLOCK) wf_logic(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
-                                                     unsigned long long* __restrict__ counters) {
+__global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
+                                                     uint32_t routed, unsigned long long* __restrict__ counters) {
   extern __shared__ float s_tables[];
   const float *spectra, *cie;
   wf_tables(sc, w, s_tables, spectra, cie);
-  const uint32_t n_cur = it == 0 ? ck.n_slots : w.iter[it].n_bounce;
+  // Routed forms (`routed` = WF_LIVE_ROUTED or WF_LIVE_CLASS): the live slots arrive in two lists -- the finish list (extension ray missed, or only an NEE
+  // answer was outstanding: these lanes finish the path and start the next one) padded to whole warps, then the bounce
+  // list (surface hit: these lanes shade) -- so the lanes of a warp are in the same phase of this kernel.  wf_emit and
+  // wf_traverse sort the slots into the two lists by their final hit (WF_LIVE_ROUTED), or wf_partition builds them in slot
+  // order from the class bytes (WF_LIVE_CLASS).  Unrouted (WF_LIVE_LIST): one live list (bounce), phases mixed.
+  const uint32_t n_fin = (routed && it != 0) ? w.iter[it].n_finish : 0u;
+  const uint32_t n_fin_pad = (n_fin + 31u) & ~31u;
+  const uint32_t n_cur = it == 0 ? ck.n_slots : n_fin_pad + w.iter[it].n_bounce;
   const uint32_t* __restrict__ cur = (it & 1u) ? w.bounce[1] : w.bounce[0];
+  const uint32_t* __restrict__ fin = (it & 1u) ? w.finish[1] : w.finish[0];
   const uint32_t total_work = ck.n_units * ck.n_samples;   // item = ordinal * n_units + unit (sample-major)
   const uint32_t lane = threadIdx.x & 31u;
   Stats st;
@@ -501,17 +534,18 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK) wf_logic(const __grid_constant
     PathState ps;
     Rng rng;
     NeeQuery nee; nee.pending = false; nee.light_prim = 0;
-    if (i < n_cur) {
+    const bool valid = i < n_cur && (i >= n_fin_pad || i < n_fin);   // not a padding lane of the finish list
+    if (valid) {
       need = true;
       if (it == 0) {
         slot = i;
       } else {
-        slot = cur[i];
+        slot = i < n_fin_pad ? fin[i] : cur[i - n_fin_pad];
         wf_load(w, slot, ps, rng, wid, flags);
         if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // before anything else is added to L
         int r = 0;
         if (!(flags & WF_FLAG_DEAD)) {
-          const float4 hv = wf_f4(w, slot, WF_R_H);
+          const float4 hv = rec_ld(w, slot, WF_R_H);
           Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
           uint32_t term = 0;
           r = wf_bounce<STATS>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
@@ -524,15 +558,28 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK) wf_logic(const __grid_constant
         if (!alive) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
       }
     }
-    // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item: one atomic per warp
+    // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item.  The first ck.n_static items of
+    // the chunk are dealt out statically -- slot s owns s, s + n_slots, s + 2 n_slots, ... -- so taking one of them needs no
+    // atomic (and no round trip to the one address every warp of the grid is adding to); the rest of the chunk is handed
+    // out through the counter, which keeps the slots busy to the end whatever their paths' lengths were.  Which slot renders
+    // an item never shows in the result (the sample is staged by item).
+#if WF_STATIC_WORK
+    if (it == 0) wid = slot - ck.n_slots;   // so that the first candidate below is item `slot`
+#endif
     for (;;) {
-      const uint32_t mask = __ballot_sync(0xffffffffu, need);
-      if (mask == 0u) break;
-      uint32_t first = 0;
-      if (lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
-      first = __shfl_sync(0xffffffffu, first, __ffs(mask) - 1);
+      bool dyn = need;
+#if WF_STATIC_WORK
+      if (need && wid + ck.n_slots < ck.n_static) { wid += ck.n_slots; dyn = false; }
+#endif
+      if (__ballot_sync(0xffffffffu, need) == 0u) break;
+      const uint32_t mask = __ballot_sync(0xffffffffu, dyn);
+      if (mask != 0u) {   // one atomic per warp
+        uint32_t first = 0;
+        if (lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
+        first = __shfl_sync(0xffffffffu, first, __ffs(mask) - 1);
+        if (dyn) wid = ck.n_static + first + __popc(mask & ((1u << lane) - 1u));
+      }
       if (need) {
-        wid = first + __popc(mask & ((1u << lane) - 1u));
         if (wid >= total_work) {
           need = false;   // the chunk has no work left: this slot retires
         } else {
@@ -547,7 +594,7 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK) wf_logic(const __grid_constant
         }
       }
     }
-    wf_emit<STATS, false>(sc, w, it, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
+    wf_emit<STATS>(sc, w, it, routed, valid, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
   }
   wf_counts_flush<STATS>(lc, st, counters);
 }
@@ -590,12 +637,15 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 // next node or triangle changes nothing; one merged fetch phase per trip -- triangle lanes and node lanes load through the
 // same registers and the warp waits once -- is equal on mesh1m and 5 % slower on the 10M soup.)  Arithmetic per node and per triangle is wide_node / wide_tri
 // (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
+#ifndef WF_TRI2
+#define WF_TRI2 0
+#endif
 #ifndef WF_REFILL_MIN
 #define WF_REFILL_MIN 8
 #endif
 template <bool STATS, bool ROUTE>
 __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(const __grid_constant__ DevScene sc, const WfState w, uint32_t it,
-                                                        unsigned long long* __restrict__ counters) {
+                                                        uint32_t fix_class, unsigned long long* __restrict__ counters) {
   __shared__ uint32_t s_done[WF_BLOCK / 32][2][64];
   const uint32_t n_ext = w.iter[it].n_bvh;
   const uint32_t n = n_ext + w.iter[it].n_shadow;   // one fetch cursor over both queues: extension rays first
@@ -617,7 +667,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
   uint2 stack[CRT_BVH_STACK];
   int sp = 0;
   uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);   // node group and triangle group of the lane's ray (crt_device.cuh)
-  bool have = false, exhausted = false, anyhit = false;
+  bool have = false, exhausted = false, anyhit = false, lin_miss = false;
   uint32_t slot = 0, exclude = CRT_MAX_U32, light_prim = 0;
   V3 d = v3(0.0f, 0.0f, 1.0f);
   WideRay r = wide_ray(v3(0.0f, 0.0f, 0.0f), d);
@@ -643,20 +693,21 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
         } else {
           anyhit = q >= n_ext;
           slot = anyhit ? w.shadow_list[q - n_ext] : queue[q];
-          const float4 a = wf_f4(w, slot, WF_R_S0);
-          const uint4 m = wf_u4(w, slot, WF_R_S5);
+          const float4 a = rec_ld(w, slot, WF_R_S0);
+          const uint4 m = rec_ldu(w, slot, WF_R_S5);
           exclude = m.x;
           if (anyhit) {
             // the NEE shadow ray: the light (linear list) is the closest hit so far at distance b.w; any triangle accepted
             // under the tie rule within that bound occludes it (crt_device.cuh shadow_intersect)
-            const float4 b = wf_f4(w, slot, WF_R_S6);
+            const float4 b = rec_ld(w, slot, WF_R_S6);
             d = v3(b);
             light_prim = m.z;
             h.t = b.w; h.idx = light_prim; h.ref = 0;
           } else {
-            const float4 b = wf_f4(w, slot, WF_R_S1), hv = wf_f4(w, slot, WF_R_H);
+            const float4 b = rec_ld(w, slot, WF_R_S1), hv = rec_ld(w, slot, WF_R_H);
             d = v3(b);
             h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
+            lin_miss = h.idx == CRT_MAX_U32;
           }
           r = wide_ray(v3(a), d);
           G = make_uint2(0u, r.valid ? 0x80000000u : 0u);   // the root as the only child of a virtual group
@@ -670,10 +721,27 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     if (__ballot_sync(0xffffffffu, have) == 0u) break;
     // ---- triangle step: one triangle for every lane that has some left
     bool done = false;
+#if WF_TRI2
+    // two triangles per trip for the lanes that have two left: both fetches are in flight together
+    if (have && T.y != 0u) {
+      const uint32_t k1 = (uint32_t)__ffs(T.y) - 1u;
+      T.y &= T.y - 1u;
+      const bool two = T.y != 0u;
+      const uint32_t k2 = two ? (uint32_t)__ffs(T.y) - 1u : k1;
+      T.y &= T.y - 1u;   // no-op when T.y is already 0
+      const uint32_t s1 = T.x + k1, s2 = T.x + k2;
+      const float4 A0 = ld_tri(&tris[3 * s1 + 0]), A1 = ld_tri(&tris[3 * s1 + 1]), A2 = ld_tri(&tris[3 * s1 + 2]);
+      const float4 B0 = ld_tri(&tris[3 * s2 + 0]), B1 = ld_tri(&tris[3 * s2 + 1]), B2 = ld_tri(&tris[3 * s2 + 2]);
+      if (STATS) ray_tris += two ? 2u : 1u;
+      if (wide_tri_eval<STATS>(A0, A1, A2, s1, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
+      else if (two && wide_tri_eval<STATS>(B0, B1, B2, s2, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
+    }
+#else
     if (have && T.y != 0u) {
       if (STATS) ray_tris++;
       if (wide_tri<STATS>(tris, T, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
     }
+#endif
     // ---- node step, for the lanes whose triangle group is (now) empty: take the nearest unvisited child of the current
     //      node group (or of the group on top of the stack), fetch it and test its 8 child boxes
     if (have && !done && T.y == 0u) {
@@ -704,13 +772,14 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     }
     if (done) {
       if (anyhit) {
-        if (h.idx != light_prim) reinterpret_cast<float*>(&wf_f4(w, slot, WF_R_S6))[3] = -1.0f;   // occluded
+        if (h.idx != light_prim) st_stream1(reinterpret_cast<float*>(rec_ptr(w, slot, WF_R_S6)) + 3, -1.0f);   // occluded
       } else {
-        wf_f4(w, slot, WF_R_H) = make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f);
+        rec_st(w, slot, WF_R_H, make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f));
+        if (fix_class && lin_miss && h.idx != CRT_MAX_U32) w.cls[slot] = (uint8_t)0;   // WF_LIVE_CLASS: a triangle turned the miss into a hit
       }
       have = false;
     }
-    if (ROUTE) {   // three-kernel form: the slot joins the next shade or finish queue by its final hit
+    if (ROUTE && __ballot_sync(0xffffffffu, fin_ext) != 0u) {   // routed forms: the slot joins the next bounce or finish queue by its final hit
       done_add(db_b, fin_ext && h.idx != CRT_MAX_U32, slot, list_b, &w.iter[it + 1u].n_bounce);
       done_add(db_f, fin_ext && h.idx == CRT_MAX_U32, slot, list_f, &w.iter[it + 1u].n_finish);
     }
@@ -731,6 +800,23 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
   }
 }
 
+// WF_LIVE_CLASS: the bounce and finish lists of iteration it + 1 from the class bytes, in slot order (one thread per slot,
+// one atomic per warp and list: warps arrive roughly in order, which is all wf_logic's record stream needs to stay
+// sequential in memory).
+__global__ void __launch_bounds__(256) wf_partition(const WfState w, uint32_t n_slots, uint32_t it) {
+  uint32_t* const list_b = ((it + 1u) & 1u) ? w.bounce[1] : w.bounce[0];
+  uint32_t* const list_f = ((it + 1u) & 1u) ? w.finish[1] : w.finish[0];
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const uint32_t n_round = (n_slots + 31u) & ~31u;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    const uint32_t c = i < n_slots ? (uint32_t)w.cls[i] : 2u;
+    const PushTicket tb = wf_reserve(c == 0u, &w.iter[it + 1u].n_bounce);
+    const PushTicket tf = wf_reserve(c == 1u, &w.iter[it + 1u].n_finish);
+    wf_commit(tb, c == 0u, i, list_b);
+    wf_commit(tf, c == 1u, i, list_f);
+  }
+}
+
 // acc += sample_1, += sample_2, ... in frame order (CS:108 over the chunk's frames), then the epilogue of
 // main (CS:109-115) with the frame counter after the chunk.
 __global__ void wf_accumulate(const __grid_constant__ DevScene sc, const WfChunk ck, float4* __restrict__ acc, uint32_t* __restrict__ fb,
@@ -742,7 +828,7 @@ __global__ void wf_accumulate(const __grid_constant__ DevScene sc, const WfChunk
   const uint32_t pix = px + py * sc.W;
   float4 a = acc[pix];
   for (uint32_t j = 0; j < ck.n_samples; j++) {
-    const float4 v = ck.stage[(size_t)j * ck.n_pixels + pix];
+    const float4 v = ld_stream(&ck.stage[(size_t)j * ck.n_pixels + pix]);
     a.x += v.x; a.y += v.y; a.z += v.z;
   }
   acc[pix] = a;
@@ -769,10 +855,10 @@ cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* sh
 #undef CRT_WF_CFG
 }
 
-cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s) {
-  if (stats) wf_logic<true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, ck, it, counters);
-  else wf_logic<false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  if (stats) wf_logic<true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, ck, it, live_mode, counters);
+  else wf_logic<false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, ck, it, live_mode, counters);
   return cudaGetLastError();
 }
 
@@ -790,15 +876,21 @@ cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk&
   return cudaGetLastError();
 }
 
-cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, int grid, uint32_t it, unsigned long long* counters,
-                               cudaStream_t s) {
+cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, bool fix_class, int grid, uint32_t it,
+                               unsigned long long* counters, cudaStream_t s) {
+  const uint32_t fc = fix_class ? 1u : 0u;
   if (stats) {
-    if (route) wf_traverse<true, true><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
-    else wf_traverse<true, false><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
+    if (route) wf_traverse<true, true><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, fc, counters);
+    else wf_traverse<true, false><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, fc, counters);
   } else {
-    if (route) wf_traverse<false, true><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
-    else wf_traverse<false, false><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, counters);
+    if (route) wf_traverse<false, true><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, fc, counters);
+    else wf_traverse<false, false><<<grid, WF_BLOCK, 0, s>>>(sc, w, it, fc, counters);
   }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_wf_partition(const WfState& w, uint32_t n_slots, int grid, uint32_t it, cudaStream_t s) {
+  wf_partition<<<grid, 256, 0, s>>>(w, n_slots, it);
   return cudaGetLastError();
 }
 

@@ -29,6 +29,7 @@ struct WfState {
   uint32_t* regen;     // slots freed by wf_shade in the current iteration
   uint32_t* bvh_list;  // [slots] slots whose extension ray must traverse the BVH
   uint32_t* shadow_list; // [slots] slots whose NEE shadow ray must (kept apart so that warps hold rays of one kind)
+  uint8_t* cls;        // [slots] class of the slot's next pass (live mode 2): 0 bounce, 1 finish, 2 retired
   WfIter* iter;        // [CRT_WF_MAX_ITERS + 2]
   uint32_t* work;      // next unassigned (sample, pixel) work item of the chunk
   uint32_t tables_in_smem;
@@ -44,6 +45,7 @@ struct WfChunk {
   uint32_t s_first;     // frame number of ordinal 0
   uint32_t s_stride;    // frame number step between ordinals (world size under split-spp, else 1)
   uint32_t n_pixels;    // W * H: stride of the staging buffer
+  uint32_t n_static;    // work items [0, n_static) are dealt to the slots statically (slot s: s, s + n_slots, ...); a multiple of n_slots
   float4* stage;        // [n_samples][n_pixels]: XYZ of each finished path, summed in order by wf_accumulate
 };
 
@@ -52,13 +54,15 @@ size_t wf_tables_bytes(const DevScene& sc);
 // resident blocks per SM of wf_logic / wf_shade / wf_regen / wf_traverse
 cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* shade_blocks_per_sm, int* regen_blocks_per_sm,
                       int* trav_blocks_per_sm);
-cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+// live_mode: 0 one live list, 1 routed lists (pushed by wf_logic and wf_traverse), 2 class bytes + wf_partition (crt_wavefront.cu)
+cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
-cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, int grid, uint32_t it, unsigned long long* counters,
-                               cudaStream_t s);
+cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, bool fix_class, int grid, uint32_t it,
+                               unsigned long long* counters, cudaStream_t s);
+cudaError_t launch_wf_partition(const WfState& w, uint32_t n_slots, int grid, uint32_t it, cudaStream_t s);
 cudaError_t launch_wf_accumulate(const DevScene& sc, const WfChunk& ck, float4* acc, uint32_t* fb, uint32_t sample_after, cudaStream_t s);
 }  // namespace crt

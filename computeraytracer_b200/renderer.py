@@ -34,7 +34,7 @@ COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits"
 SHARD_NONE, SHARD_TILES, SHARD_SPLIT_SPP = 0, 1, 2
 KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
 FLAG_STATS, FLAG_KERNEL_TIMES, FLAG_WF_SPLIT = 1, 2, 4
-KERNEL_CLASSES = ["wf_logic", "wf_traverse", "wf_accumulate", "pt_megakernel", "wf_regen", "wf_shade"]
+KERNEL_CLASSES = ["wf_logic", "wf_traverse", "wf_accumulate", "pt_megakernel", "wf_regen", "wf_shade", "wf_partition"]
 
 STATUS = {0: "CRT_OK", 1: "CRT_ERR_ARG", 2: "CRT_ERR_BINDING", 3: "CRT_ERR_SIZE", 4: "CRT_ERR_STATE",
           5: "CRT_ERR_CUDA", 6: "CRT_ERR_OOM", 7: "CRT_ERR_NODEVICE"}

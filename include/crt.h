@@ -94,7 +94,8 @@ enum crt_kernel_class {
   CRT_KC_MEGA = 3,          /* pt_megakernel                                                 */
   CRT_KC_WF_REGEN = 4,      /* wf_regen: finish ended paths, start new ones on free slots    */
   CRT_KC_WF_SHADE = 5,      /* wf_shade: one bounce per slot of the shade queue (split form) */
-  CRT_NUM_KERNEL_CLASSES = 6
+  CRT_KC_WF_PARTITION = 6,  /* wf_partition: bounce and finish lists from the slots' class bytes */
+  CRT_NUM_KERNEL_CLASSES = 7
 };
 
 #define CRT_NUM_COUNTERS 16
