@@ -322,8 +322,8 @@ int prepare(crt_ctx* ctx) {
 }
 
 #ifndef CRT_WF_LIVE_BVH
-#define CRT_WF_LIVE_BVH 0      // live mode for scenes with triangles
-#endif
+#define CRT_WF_LIVE_BVH 2      // live mode for scenes with triangles (mesh1m: 351.5 -> 341.4 ms per 256-spp step; 1 is 40 % slower:
+#endif                        // lists filled by wf_traverse lose the slot order and with it the sequential record stream)
 #ifndef CRT_WF_LIVE_LINEAR
 #define CRT_WF_LIVE_LINEAR 1   // live mode for linear-list scenes (reference default scene 1080p x 64 frames: 64.8 -> 55.0 ms)
 #endif
@@ -401,6 +401,11 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   uint32_t live_mode = s.n_tri ? CRT_WF_LIVE_BVH : CRT_WF_LIVE_LINEAR;
   if (const char* e = getenv("CRT_WF_ROUTED")) live_mode = (uint32_t)atoi(e) % 3u;   // tuning override
   if (split) live_mode = 0;
+  // routed forms: paths that end in a bounce warp are finished by the next iteration's finish warps (mesh1m: 339.8 ->
+  // 334.5 ms per step; the reference default scene: 56.0 -> 58.0 ms, so linear-list scenes finish in place)
+  uint32_t defer = s.n_tri ? 1u : 0u;
+  if (const char* e = getenv("CRT_WF_DEFER")) defer = atoi(e) != 0;   // tuning override
+  const uint32_t logic_mode = live_mode | ((live_mode && defer) ? 0x100u : 0u);
   uint32_t static_eighths = CRT_WF_STATIC_EIGHTHS;
   if (const char* e = getenv("CRT_WF_STATIC")) static_eighths = std::min<uint32_t>((uint32_t)strtoul(e, nullptr, 10), 8u);   // tuning override
   uint32_t left = n;
@@ -443,7 +448,7 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       for (;;) {
         if (!split) {
           CU(mark(ctx, CRT_KC_WF_LOGIC));
-          CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, live_mode, grid_l, smem, it, ctx->d_counters, ctx->stream));
+          CU(crt::launch_wf_logic(s, ctx->wf, ck, stats, logic_mode, grid_l, smem, it, ctx->d_counters, ctx->stream));
           ctx->launches++;
         } else {
           if (it) {
