@@ -400,7 +400,7 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   // are in one phase.
   uint32_t live_mode = s.n_tri ? CRT_WF_LIVE_BVH : CRT_WF_LIVE_LINEAR;
   if (const char* e = getenv("CRT_WF_ROUTED")) live_mode = (uint32_t)atoi(e) % 3u;   // tuning override
-  if (split) live_mode = 0;
+  if (split && live_mode == 0) live_mode = 1;   // the split kernels always work over routed lists: filled as rays finish (1) or by wf_partition (2)
   // routed forms: paths that end in a bounce warp are finished by the next iteration's finish warps (mesh1m: 339.8 ->
   // 334.5 ms per step; the reference default scene: 56.0 -> 58.0 ms, so linear-list scenes finish in place)
   uint32_t defer = s.n_tri ? 1u : 0u;
@@ -453,16 +453,16 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
         } else {
           if (it) {
             CU(mark(ctx, CRT_KC_WF_SHADE));
-            CU(crt::launch_wf_shade(s, ctx->wf, ck, stats, grid_s, smem, it, ctx->d_counters, ctx->stream));
+            CU(crt::launch_wf_shade(s, ctx->wf, ck, stats, live_mode, grid_s, smem, it, ctx->d_counters, ctx->stream));
             ctx->launches++;
           }
           CU(mark(ctx, CRT_KC_WF_REGEN));
-          CU(crt::launch_wf_regen(s, ctx->wf, ck, stats, grid_r, smem, it, ctx->d_counters, ctx->stream));
+          CU(crt::launch_wf_regen(s, ctx->wf, ck, stats, live_mode, grid_r, smem, it, ctx->d_counters, ctx->stream));
           ctx->launches++;
         }
         if (s.n_tri) {
           CU(mark(ctx, CRT_KC_WF_TRAVERSE));
-          CU(crt::launch_wf_traverse(s, ctx->wf, stats, split || live_mode == 1, live_mode == 2, grid_t, it, ctx->d_counters, ctx->stream));
+          CU(crt::launch_wf_traverse(s, ctx->wf, stats, live_mode == 1, live_mode == 2, grid_t, it, ctx->d_counters, ctx->stream));
           ctx->launches++;
         }
         if (live_mode == 2) {

@@ -392,7 +392,7 @@ __device__ __forceinline__ void wf_tables(const DevScene& sc, const WfState& w, 
 #endif
 template <bool STATS>
 __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
-                                                     unsigned long long* __restrict__ counters) {
+                                                     uint32_t live_mode, unsigned long long* __restrict__ counters) {
   extern __shared__ float s_tables[];
   const float *spectra, *cie;
   wf_tables(sc, w, s_tables, spectra, cie);
@@ -425,7 +425,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
       if (ended) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
     }
     const PushTicket tr = wf_reserve(ended, &w.iter[it].n_regen);   // in flight while wf_emit scans the linear list
-    wf_emit<STATS>(sc, w, it, WF_LIVE_ROUTED, true, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
+    wf_emit<STATS>(sc, w, it, live_mode, i < n_cur, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
     wf_commit(tr, ended, slot, w.regen);
   }
   wf_counts_flush<STATS>(lc, st, counters);
@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
 // which is cheap -- followed by the slots wf_shade freed.  A slot retires when the chunk has no work left.
 template <bool STATS>
 __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
-                                                     unsigned long long* __restrict__ counters) {
+                                                     uint32_t live_mode, unsigned long long* __restrict__ counters) {
   extern __shared__ float s_tables[];
   const float *spectra, *cie;
   wf_tables(sc, w, s_tables, spectra, cie);
@@ -496,7 +496,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
       mask = __ballot_sync(0xffffffffu, need);   // lanes that drew a unit outside the image fetch again
       if (mask != 0u && lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
     }
-    wf_emit<STATS>(sc, w, it, WF_LIVE_ROUTED, true, alive, alive, slot, ps, rng, wid, 0u, nee, st, lc);
+    wf_emit<STATS>(sc, w, it, live_mode, i < n_cur, alive, alive, slot, ps, rng, wid, 0u, nee, st, lc);
   }
   wf_counts_flush<STATS>(lc, st, counters);
 }
@@ -646,6 +646,12 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 #ifndef WF_TRI2
 #define WF_TRI2 0
 #endif
+#ifndef WF_SSTACK
+#define WF_SSTACK 8          // entries of a lane's traversal stack kept in shared memory, the rest in local memory (0 -> 8: wf_traverse -1.5 % on mesh1m, -2.6 % on soup10m; 5 = 8)
+#endif
+#ifndef WF_TRI_PREFETCH
+#define WF_TRI_PREFETCH 0    // after a node step, prefetch.global.L1 the triangles of the group that are tested in later trips
+#endif
 #ifndef WF_REFILL_MIN
 #define WF_REFILL_MIN 8
 #endif
@@ -670,7 +676,16 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
   const uint32_t one = wide_one(it);
   Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
 
+#if WF_SSTACK
+  __shared__ uint2 s_stack[WF_SSTACK][WF_BLOCK];   // [entry][thread]: a lane's column, conflict-free whatever the lanes' depths
+  uint2 stack[CRT_BVH_STACK - WF_SSTACK];
+#define WF_PUSH(g) do { if (sp < WF_SSTACK) s_stack[sp][threadIdx.x] = (g); else stack[sp - WF_SSTACK] = (g); sp++; } while (0)
+#define WF_POP(g) do { --sp; if (sp < WF_SSTACK) (g) = s_stack[sp][threadIdx.x]; else (g) = stack[sp - WF_SSTACK]; } while (0)
+#else
   uint2 stack[CRT_BVH_STACK];
+#define WF_PUSH(g) do { stack[sp++] = (g); } while (0)
+#define WF_POP(g) do { (g) = stack[--sp]; } while (0)
+#endif
   int sp = 0;
   uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);   // node group and triangle group of the lane's ray (crt_device.cuh)
   bool have = false, exhausted = false, anyhit = false, lin_miss = false;
@@ -753,13 +768,25 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     if (have && !done && T.y == 0u) {
       if (!(G.y & CRT_WIDE_HITS)) {
         if (sp == 0) done = true;
-        else G = stack[--sp];
+        else WF_POP(G);
       }
       if (!done) {
         const uint32_t node = wide_pop_child(G, r.octinv);
-        if (G.y & CRT_WIDE_HITS) stack[sp++] = G;
+        if (G.y & CRT_WIDE_HITS) WF_PUSH(G);
         wide_node<STATS>(nodes, node, r, one, t_min, h.t, G, T, st);
         if (STATS) ray_nodes++;
+#if WF_TRI_PREFETCH
+        {   // the first triangle of the group is tested in the next trip, too soon for a prefetch; the others come later
+          uint32_t m = T.y & (T.y - 1u);
+          while (m) {
+            const uint32_t k = (uint32_t)__ffs(m) - 1u;
+            m &= m - 1u;
+            const char* a = reinterpret_cast<const char*>(tris + 3u * (T.x + k));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a + 47));
+          }
+        }
+#endif
       }
     }
     // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
@@ -915,17 +942,17 @@ cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk&
   return cudaGetLastError();
 }
 
-cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s) {
-  if (stats) wf_shade<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
-  else wf_shade<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  if (stats) wf_shade<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, live_mode, counters);
+  else wf_shade<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, live_mode, counters);
   return cudaGetLastError();
 }
 
-cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s) {
-  if (stats) wf_regen<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
-  else wf_regen<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, counters);
+  if (stats) wf_regen<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, live_mode, counters);
+  else wf_regen<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, ck, it, live_mode, counters);
   return cudaGetLastError();
 }
 

@@ -57,9 +57,9 @@ cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* sh
 // live_mode: 0 one live list, 1 routed lists (pushed by wf_logic and wf_traverse), 2 class bytes + wf_partition (crt_wavefront.cu)
 cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
-cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
-cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, int grid, size_t smem, uint32_t it,
+cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, bool fix_class, int grid, uint32_t it,
                                unsigned long long* counters, cudaStream_t s);
