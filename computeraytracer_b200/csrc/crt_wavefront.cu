@@ -44,8 +44,9 @@ enum {
   WF_R_S0 = 0, WF_R_S1 = 1,   // sector A: ray origin + last_bounce_pdf, ray direction + etaScale
   WF_R_H = 2, WF_R_S5 = 3,    // sector B: hit of the extension ray; exclude, depth|flags|wavelength, sampled light's primitive, work item
   WF_R_S6 = 4, WF_R_S7 = 5,   // sector C: pending NEE shadow ray (direction, light distance) and contribution
-  WF_R_S2 = 6, WF_R_S3 = 7,   // sector D: accumulated radiance, beta
-  WF_R_S4 = 8                 // sector E: RNG state (+ 16 bytes spare)
+  WF_R_S3 = 6, WF_R_S4 = 7,   // sector D: beta, RNG state
+  WF_R_S2 = 8                 // sector E: accumulated radiance L (+ 16 bytes spare) -- on its own, because a pass touches it
+                              // only when it adds to L or finishes the path (WF_FLAG_LZERO: never written yet, reads as 0)
 };
 // Record accessors.  With CRT_L2_REC the records -- a multi-gigabyte stream that every iteration reads and rewrites once --
 // go through L2 with an evict-first policy, so that they do not push the scene (nodes, triangles) out of L2.
@@ -63,6 +64,7 @@ __device__ __forceinline__ void rec_stu(const WfState& w, uint32_t slot, int wor
 #define WF_FLAG_TRANSMISSION 2u
 #define WF_FLAG_PENDING 4u            // an NEE contribution (S7) waits for the any-hit answer of its shadow ray (S6)
 #define WF_FLAG_DEAD 8u               // Russian roulette ended the path; only the pending contribution is outstanding
+#define WF_FLAG_LZERO 0x800u          // (bit 31 of the packed word) L is still 0 and its sector has not been written for this path
 
 // unit -> pixel: units enumerate this rank's 8x4 tiles, 32 pixels each (the megakernel's unit order)
 __device__ __forceinline__ bool unit_pixel(const DevScene& sc, uint32_t unit, uint32_t& px, uint32_t& py) {
@@ -78,29 +80,33 @@ __device__ __forceinline__ void wf_load(const WfState& w, uint32_t slot, PathSta
   const float4 a = rec_ld(w, slot, WF_R_S0), b = rec_ld(w, slot, WF_R_S1);
   ps.o = v3(a); ps.pdf = a.w;
   ps.d = v3(b); ps.etaScale = b.w;
-  ps.L = rec_ld(w, slot, WF_R_S2);
+  ps.L = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // not loaded here: wf_load_L
   ps.beta = rec_ld(w, slot, WF_R_S3);
   const uint4 r = rec_ldu(w, slot, WF_R_S4);
   rng.x = r.x; rng.y = r.y; rng.z = r.z; rng.w = r.w;
   const uint4 m = rec_ldu(w, slot, WF_R_S5);
   ps.exclude = m.x;
   ps.depth = m.y & 0xFFFFu;
-  flags = (m.y >> 16) & 0xFu;
-  ps.lam0 = m.y >> 20;
+  flags = ((m.y >> 16) & 0xFu) | ((m.y >> 20) & WF_FLAG_LZERO);
+  ps.lam0 = (m.y >> 20) & 0x7FFu;
   ps.specular = (flags & WF_FLAG_SPECULAR) != 0; ps.in_transmission = (flags & WF_FLAG_TRANSMISSION) != 0;
   ps.shadow_phase = false;
   wid = m.w;
 }
 
+__device__ __forceinline__ float4 wf_load_L(const WfState& w, uint32_t slot, uint32_t flags) {
+  return (flags & WF_FLAG_LZERO) ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : rec_ld(w, slot, WF_R_S2);
+}
+
+// everything but L (the caller stores L when it changed it, and then clears WF_FLAG_LZERO)
 __device__ __forceinline__ void wf_store(const WfState& w, uint32_t slot, const PathState& ps, const Rng& rng, uint32_t wid, uint32_t flags,
                                          uint32_t light_prim) {
   rec_st(w, slot, WF_R_S0, make_float4(ps.o.x, ps.o.y, ps.o.z, ps.pdf));
   rec_st(w, slot, WF_R_S1, make_float4(ps.d.x, ps.d.y, ps.d.z, ps.etaScale));
-  rec_st(w, slot, WF_R_S2, ps.L);
   rec_st(w, slot, WF_R_S3, ps.beta);
   rec_stu(w, slot, WF_R_S4, make_uint4(rng.x, rng.y, rng.z, rng.w));
   const uint32_t fl = (flags & (WF_FLAG_PENDING | WF_FLAG_DEAD)) | (ps.specular ? WF_FLAG_SPECULAR : 0u) | (ps.in_transmission ? WF_FLAG_TRANSMISSION : 0u);
-  rec_stu(w, slot, WF_R_S5, make_uint4(ps.exclude, (ps.depth & 0xFFFFu) | (fl << 16) | (ps.lam0 << 20), light_prim, wid));
+  rec_stu(w, slot, WF_R_S5, make_uint4(ps.exclude, (ps.depth & 0xFFFFu) | (fl << 16) | (ps.lam0 << 20) | ((flags & WF_FLAG_LZERO) << 20), light_prim, wid));
 }
 
 // Appending to a global queue costs one atomic per warp, in two steps so that several queues can be served with the
@@ -272,10 +278,14 @@ __device__ __forceinline__ void wf_finish(const DevScene& sc, const WfChunk& ck,
 }
 
 // the pending NEE contribution of a slot, as the reference would have added it (CS:187 with CS:400 or CS:407)
-__device__ __forceinline__ void wf_add_pending(const WfState& w, uint32_t slot, float4& L) {
+__device__ __forceinline__ float4 wf_pending(const WfState& w, uint32_t slot) {
   const bool occluded = ld_stream1(reinterpret_cast<const float*>(rec_ptr(w, slot, WF_R_S6)) + 3) < 0.0f;   // wf_traverse marks an occluded segment by a negative length
   float4 c = rec_ld(w, slot, WF_R_S7);
   if (occluded) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407: Le = 0, the sum still happens
+  return c;
+}
+__device__ __forceinline__ void wf_add_pending(const WfState& w, uint32_t slot, float4& L) {
+  const float4 c = wf_pending(w, slot);
   L.x += c.x; L.y += c.y; L.z += c.z; L.w += c.w;
 }
 
@@ -412,6 +422,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
     if (i < n_cur) {
       slot = cur[i];
       wf_load(w, slot, ps, rng, wid, flags);
+      ps.L = wf_load_L(w, slot, flags);
       if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // before anything else is added to L
       const float4 hv = rec_ld(w, slot, WF_R_H);
       Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
@@ -423,6 +434,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
       has_ext = r == 1;
       ended = r == 0;
       if (ended) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
+      else rec_st(w, slot, WF_R_S2, ps.L);   // (the new flags carry no WF_FLAG_LZERO)
     }
     const PushTicket tr = wf_reserve(ended, &w.iter[it].n_regen);   // in flight while wf_emit scans the linear list
     wf_emit<STATS>(sc, w, it, live_mode, i < n_cur, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
@@ -464,10 +476,10 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
       } else if (i < n_fin) {
         slot = fin[i];
         const uint4 m = rec_ldu(w, slot, WF_R_S5);
-        const uint32_t flags = (m.y >> 16) & 0xFu;
-        float4 L = rec_ld(w, slot, WF_R_S2);
+        const uint32_t flags = ((m.y >> 16) & 0xFu) | ((m.y >> 20) & WF_FLAG_LZERO);
+        float4 L = wf_load_L(w, slot, flags);
         if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, L);
-        wf_finish(sc, ck, cie, L, m.y >> 20, m.w);
+        wf_finish(sc, ck, cie, L, (m.y >> 20) & 0x7FFu, m.w);
         if (STATS && !(flags & WF_FLAG_DEAD)) { lc.term_cnt[0]++; lc.depth_sum += m.y & 0xFFFFu; }
       } else {
         slot = w.regen[i - n_fin];
@@ -496,7 +508,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
       mask = __ballot_sync(0xffffffffu, need);   // lanes that drew a unit outside the image fetch again
       if (mask != 0u && lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
     }
-    wf_emit<STATS>(sc, w, it, live_mode, i < n_cur, alive, alive, slot, ps, rng, wid, 0u, nee, st, lc);
+    wf_emit<STATS>(sc, w, it, live_mode, i < n_cur, alive, alive, slot, ps, rng, wid, WF_FLAG_LZERO, nee, st, lc);
   }
   wf_counts_flush<STATS>(lc, st, counters);
 }
@@ -543,8 +555,15 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
         slot = i;
       } else {
         slot = i < n_fin_pad ? fin[i] : cur[i - n_fin_pad];
+        // L stays in memory unless this pass adds to it or finishes the path.  With an NEE answer outstanding L is
+        // needed for sure: it is loaded with the rest of the record and the sums run in place, the outstanding
+        // contribution first (the reference's order).  Otherwise ps.L starts at 0 and collects what wf_bounce adds (at
+        // most one term, CS:152 / CS:156 / CS:187; 0 + c = c), and L is fetched afterwards only if that term is not all
+        // zeros (L is never -0, so L + 0 = L bit for bit; a NaN term is not "all zeros") or the path ended.
         wf_load(w, slot, ps, rng, wid, flags);
-        if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // before anything else is added to L
+        const bool had_pending = (flags & WF_FLAG_PENDING) != 0u;
+        const uint32_t lzero = flags & WF_FLAG_LZERO;
+        if (had_pending) { ps.L = wf_load_L(w, slot, lzero); wf_add_pending(w, slot, ps.L); }
         int r = 0;
         if (!(flags & WF_FLAG_DEAD)) {
           const float4 hv = rec_ld(w, slot, WF_R_H);
@@ -557,11 +576,21 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
           // path, and the next iteration finishes it and starts its next path in a warp whose lanes all do that
           if (defer && r == 0 && i >= n_fin_pad) r = 2;
         }
-        flags = (nee.pending ? WF_FLAG_PENDING : 0u) | (r == 2 ? WF_FLAG_DEAD : 0u);
+        flags = (nee.pending ? WF_FLAG_PENDING : 0u) | (r == 2 ? WF_FLAG_DEAD : 0u) | lzero;
         alive = r != 0;
         has_ext = r == 1;
         need = !alive;
+        bool store_L = had_pending;
+        if (!had_pending) {
+          const float4 dl = ps.L;
+          const bool has_dl = !(dl.x == 0.0f && dl.y == 0.0f && dl.z == 0.0f && dl.w == 0.0f);
+          if (has_dl || !alive) {
+            ps.L = wf_load_L(w, slot, lzero);
+            if (has_dl) { ps.L.x += dl.x; ps.L.y += dl.y; ps.L.z += dl.z; ps.L.w += dl.w; store_L = true; }
+          }
+        }
         if (!alive) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
+        else if (store_L) { rec_st(w, slot, WF_R_S2, ps.L); flags &= ~WF_FLAG_LZERO; }
       }
     }
     // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item.  The first ck.n_static items of
@@ -594,7 +623,7 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
           if (unit_pixel(sc, wid - j * ck.n_units, px, py)) {   // edge tiles have units outside the image
             path_begin<STATS, true>(sc, px, py, ck.s_first + j * ck.s_stride, ps, rng, st);
             lc.n_paths++;
-            alive = true; has_ext = true; flags = 0; nee.pending = false;
+            alive = true; has_ext = true; flags = WF_FLAG_LZERO; nee.pending = false;
             need = false;
           }
         }
