@@ -240,7 +240,7 @@ int upload_scene(crt_ctx* ctx) {
     s.lin_g = ctx->d_lin;
   }
   if (s.n_tri) {
-    // one allocation, nodes first: an L2 access-policy window (below) is a single address range
+    // one allocation, nodes first
     const size_t node_bytes = (bvh.nodes.size() * 4 + 255) & ~(size_t)255, tri_bytes = (size_t)s.n_tri * 48;
     CU(cudaMalloc(&ctx->d_nodes, node_bytes + tri_bytes));
     ctx->d_tri = (float4*)((uint8_t*)ctx->d_nodes + node_bytes);
@@ -272,32 +272,6 @@ int upload_scene(crt_ctx* ctx) {
     }
     if (s.shadow_closest) break;
   }
-  // CRT_L2_PERSIST=1 (tuning): keep nodes and triangles in the persisting part of L2 while the wavefront kernels stream
-  // the slot records through the rest.  The window covers the nodes first; if the scene is larger than the persisting
-  // carve-out, hitRatio scales the share of lines that are kept.
-  {
-    const char* e = getenv("CRT_L2_PERSIST");
-    cudaStreamAttrValue attr;
-    memset(&attr, 0, sizeof(attr));
-    if (e && atoi(e) > 0 && ctx->scene_bytes) {
-      cudaDeviceProp prop;
-      int dev = 0;
-      CU(cudaGetDevice(&dev));
-      CU(cudaGetDeviceProperties(&prop, dev));
-      const size_t carve = std::min<size_t>((size_t)prop.persistingL2CacheMaxSize, ctx->scene_bytes);
-      const size_t win = std::min<size_t>((size_t)prop.accessPolicyMaxWindowSize, atoi(e) == 2 ? (size_t)s.n_nodes * 16 * CRT_NODE_STRIDE : ctx->scene_bytes);
-      if (carve && win) {
-        CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
-        attr.accessPolicyWindow.base_ptr = ctx->d_nodes;
-        attr.accessPolicyWindow.num_bytes = win;
-        attr.accessPolicyWindow.hitRatio = win <= carve ? 1.0f : (float)((double)carve / (double)win);
-        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
-        fprintf(stderr, "[crt] L2 persisting window: %zu bytes, carve-out %zu of max %d, hit ratio %.2f\n", win, carve, prop.persistingL2CacheMaxSize, attr.accessPolicyWindow.hitRatio);
-      }
-    }
-    CU(cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
-  }
   const auto t1 = std::chrono::steady_clock::now();
   ctx->stats[0] = n_prims; ctx->stats[1] = s.n_lin; ctx->stats[2] = s.n_tri; ctx->stats[3] = s.n_nodes;
   ctx->stats[4] = (uint64_t)s.n_nodes * 16 * CRT_NODE_STRIDE; ctx->stats[5] = (uint64_t)s.n_tri * 48;
@@ -326,9 +300,6 @@ int prepare(crt_ctx* ctx) {
 #endif                        // lists filled by wf_traverse lose the slot order and with it the sequential record stream)
 #ifndef CRT_WF_LIVE_LINEAR
 #define CRT_WF_LIVE_LINEAR 1   // live mode for linear-list scenes (reference default scene 1080p x 64 frames: 64.8 -> 55.0 ms)
-#endif
-#ifndef CRT_WF_STATIC_EIGHTHS
-#define CRT_WF_STATIC_EIGHTHS 0
 #endif
 constexpr size_t kWfCounterBytes = (size_t)(CRT_WF_MAX_ITERS + 2) * sizeof(WfIter) + 64;   // iteration records + the work counter
 
@@ -406,8 +377,6 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   uint32_t defer = s.n_tri ? 1u : 0u;
   if (const char* e = getenv("CRT_WF_DEFER")) defer = atoi(e) != 0;   // tuning override
   const uint32_t logic_mode = live_mode | ((live_mode && defer) ? 0x100u : 0u);
-  uint32_t static_eighths = CRT_WF_STATIC_EIGHTHS;
-  if (const char* e = getenv("CRT_WF_STATIC")) static_eighths = std::min<uint32_t>((uint32_t)strtoul(e, nullptr, 10), 8u);   // tuning override
   uint32_t left = n;
   while (left) {
     const uint32_t k = left < chunk ? left : chunk;
@@ -430,8 +399,6 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       chunk = std::max(1u, k / 2);
       continue;
     }
-    // static share of the work items (eighths of the whole rounds of the pool; wf_logic only): see wf_logic's work loop
-    ck.n_static = split ? 0u : (uint32_t)((total_work / ck.n_slots) * static_eighths / 8u) * ck.n_slots;
     const size_t stage_bytes = (size_t)std::max(1u, ck.n_samples) * n_pixels * 16;
     if (stage_bytes > ctx->wf_stage_bytes) {
       if (ctx->wf_stage) { cudaFree(ctx->wf_stage); ctx->wf_stage = nullptr; ctx->wf_stage_bytes = 0; }

@@ -81,79 +81,6 @@ struct Stats {
   uint32_t prim_tests, node_visits, tri_tests, rand_calls;
 };
 
-// ------------------------------------------------------------------------------------------------ L2 residency hints
-// The wavefront kernels stream gigabytes of slot records, queues and staged samples through the same L2 (126 MB) that
-// holds the scene.  createpolicy + ld/st.L2::cache_hint tell the L2 what to keep: nodes (and triangles) evict-last,
-// the streams evict-first.  Switches: CRT_L2_NODES / CRT_L2_TRIS (1 = evict_last), CRT_L2_REC (1 = evict_first).
-#ifndef CRT_L2_NODES
-#define CRT_L2_NODES 0
-#endif
-#ifndef CRT_L2_TRIS
-#define CRT_L2_TRIS 0
-#endif
-#ifndef CRT_L2_REC
-#define CRT_L2_REC 0
-#endif
-__device__ __forceinline__ uint64_t l2_evict_last() { uint64_t p; asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p; }
-__device__ __forceinline__ uint64_t l2_evict_first() { uint64_t p; asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p; }
-__device__ __forceinline__ uint4 ldg_keep(const uint4* a) {
-  uint4 v;
-  asm("ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(a), "l"(l2_evict_last()));
-  return v;
-}
-__device__ __forceinline__ float4 ldg_keep(const float4* a) {
-  float4 v;
-  asm("ld.global.nc.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(a), "l"(l2_evict_last()));
-  return v;
-}
-__device__ __forceinline__ uint4 ld_node(const uint4* a) {
-#if CRT_L2_NODES
-  return ldg_keep(a);
-#else
-  return __ldg(a);
-#endif
-}
-__device__ __forceinline__ float4 ld_tri(const float4* a) {
-#if CRT_L2_TRIS
-  return ldg_keep(a);
-#else
-  return __ldg(a);
-#endif
-}
-// read-write streams (slot records, staged samples)
-__device__ __forceinline__ float4 ld_stream(const float4* a) {
-#if CRT_L2_REC
-  float4 v;
-  asm volatile("ld.global.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(a), "l"(l2_evict_first()));
-  return v;
-#else
-  return *a;
-#endif
-}
-__device__ __forceinline__ float ld_stream1(const float* a) {
-#if CRT_L2_REC
-  float v;
-  asm volatile("ld.global.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(a), "l"(l2_evict_first()));
-  return v;
-#else
-  return *a;
-#endif
-}
-__device__ __forceinline__ void st_stream(float4* a, float4 v) {
-#if CRT_L2_REC
-  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(l2_evict_first()) : "memory");
-#else
-  *a = v;
-#endif
-}
-__device__ __forceinline__ void st_stream1(float* a, float v) {
-#if CRT_L2_REC
-  asm volatile("st.global.L2::cache_hint.f32 [%0], %1, %2;" ::"l"(a), "f"(v), "l"(l2_evict_first()) : "memory");
-#else
-  *a = v;
-#endif
-}
-
 // ------------------------------------------------------------------------------------------------ vectors
 struct V3 { float x, y, z; };
 __device__ __forceinline__ V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
@@ -386,11 +313,11 @@ __device__ __forceinline__ void wide_node_eval(const uint4 w0, const uint4 w1, c
 template <bool STATS>
 __device__ __forceinline__ void wide_node(const uint4* __restrict__ nodes, uint32_t node, const WideRay& r, uint32_t one, float t_min,
                                           float t_max, uint2& G, uint2& T, Stats& st) {
-  const uint4 w0 = ld_node(&nodes[CRT_NODE_STRIDE * node + 0]);
-  const uint4 w1 = ld_node(&nodes[CRT_NODE_STRIDE * node + 1]);
-  const uint4 w2 = ld_node(&nodes[CRT_NODE_STRIDE * node + 2]);
-  const uint4 w3 = ld_node(&nodes[CRT_NODE_STRIDE * node + 3]);
-  const uint4 w4 = ld_node(&nodes[CRT_NODE_STRIDE * node + 4]);
+  const uint4 w0 = __ldg(&nodes[CRT_NODE_STRIDE * node + 0]);
+  const uint4 w1 = __ldg(&nodes[CRT_NODE_STRIDE * node + 1]);
+  const uint4 w2 = __ldg(&nodes[CRT_NODE_STRIDE * node + 2]);
+  const uint4 w3 = __ldg(&nodes[CRT_NODE_STRIDE * node + 3]);
+  const uint4 w4 = __ldg(&nodes[CRT_NODE_STRIDE * node + 4]);
   wide_node_eval<STATS>(w0, w1, w2, w3, w4, r, one, t_min, t_max, G, T, st);
 }
 
@@ -413,9 +340,9 @@ __device__ __forceinline__ bool wide_tri(const float4* __restrict__ tris, uint2&
   const uint32_t k = (uint32_t)__ffs(T.y) - 1u;
   T.y &= T.y - 1u;
   const uint32_t slot = T.x + k;
-  const float4 T0 = ld_tri(&tris[3 * slot + 0]);
-  const float4 T1 = ld_tri(&tris[3 * slot + 1]);
-  const float4 T2 = ld_tri(&tris[3 * slot + 2]);
+  const float4 T0 = __ldg(&tris[3 * slot + 0]);
+  const float4 T1 = __ldg(&tris[3 * slot + 1]);
+  const float4 T2 = __ldg(&tris[3 * slot + 2]);
   return wide_tri_eval<STATS>(T0, T1, T2, slot, o, d, exclude, t_min, anyhit, h, st);
 }
 
@@ -529,8 +456,8 @@ __device__ __forceinline__ Surface surface_of(const DevScene& sc, const Hit& h, 
   s.position = madd(o, h.t, d);                       // ray_at, CS:304-307
   if (h.ref & CRT_TRI_REF) {
     const uint32_t slot = h.ref & ~CRT_TRI_REF;
-    const float4 T1 = ld_tri(&sc.tri[3 * slot + 1]);
-    const float4 T2 = ld_tri(&sc.tri[3 * slot + 2]);
+    const float4 T1 = __ldg(&sc.tri[3 * slot + 1]);
+    const float4 T2 = __ldg(&sc.tri[3 * slot + 2]);
     V3 n = normalize(cross(v3(T1), v3(T2)));
     if (dot(n, d) > 0.0f) n = -n;
     s.normal = n;

@@ -32,9 +32,6 @@
 #ifndef WF_LOGIC_MIN_BLOCKS
 #define WF_LOGIC_MIN_BLOCKS 3   // 3 x 256 threads per SM = 85 registers at most (ptxas picks 106 without the bound)
 #endif
-#ifndef WF_STATIC_WORK
-#define WF_STATIC_WORK 1   // wf_logic honours WfChunk::n_static (0 = every work item through the global counter)
-#endif
 
 // One slot's record: WF_REC_WORDS 16-byte words, contiguous, so that every 32-byte DRAM sector a kernel touches is used
 // in full (the first version kept one array per word: each access pulled a half-used sector from a different DRAM page,
@@ -48,18 +45,13 @@ enum {
   WF_R_S2 = 8                 // sector E: accumulated radiance L (+ 16 bytes spare) -- on its own, because a pass touches it
                               // only when it adds to L or finishes the path (WF_FLAG_LZERO: never written yet, reads as 0)
 };
-// Record accessors.  With CRT_L2_REC the records -- a multi-gigabyte stream that every iteration reads and rewrites once --
-// go through L2 with an evict-first policy, so that they do not push the scene (nodes, triangles) out of L2.
+// Record accessors.  (Measured and rejected: sending the record stream through L2 with an evict-first policy -- wf_traverse
+// and the next wf_logic find the records in L2 today, profiles/r01t_static_l2_tri2_variants.txt.)
 __device__ __forceinline__ float4* rec_ptr(const WfState& w, uint32_t slot, int word) { return &w.rec[(size_t)slot * WF_REC_WORDS + word]; }
-__device__ __forceinline__ float4 rec_ld(const WfState& w, uint32_t slot, int word) { return ld_stream(rec_ptr(w, slot, word)); }
-__device__ __forceinline__ uint4 rec_ldu(const WfState& w, uint32_t slot, int word) {
-  const float4 v = rec_ld(w, slot, word);
-  return make_uint4(__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
-}
-__device__ __forceinline__ void rec_st(const WfState& w, uint32_t slot, int word, float4 v) { st_stream(rec_ptr(w, slot, word), v); }
-__device__ __forceinline__ void rec_stu(const WfState& w, uint32_t slot, int word, uint4 v) {
-  rec_st(w, slot, word, make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w)));
-}
+__device__ __forceinline__ float4 rec_ld(const WfState& w, uint32_t slot, int word) { return *rec_ptr(w, slot, word); }
+__device__ __forceinline__ uint4 rec_ldu(const WfState& w, uint32_t slot, int word) { return *reinterpret_cast<const uint4*>(rec_ptr(w, slot, word)); }
+__device__ __forceinline__ void rec_st(const WfState& w, uint32_t slot, int word, float4 v) { *rec_ptr(w, slot, word) = v; }
+__device__ __forceinline__ void rec_stu(const WfState& w, uint32_t slot, int word, uint4 v) { *reinterpret_cast<uint4*>(rec_ptr(w, slot, word)) = v; }
 #define WF_FLAG_SPECULAR 1u
 #define WF_FLAG_TRANSMISSION 2u
 #define WF_FLAG_PENDING 4u            // an NEE contribution (S7) waits for the any-hit answer of its shadow ray (S6)
@@ -274,12 +266,12 @@ __device__ __forceinline__ void wf_finish(const DevScene& sc, const WfChunk& ck,
   const uint32_t j = wid / ck.n_units;
   uint32_t px, py;
   unit_pixel(sc, wid - j * ck.n_units, px, py);
-  st_stream(&ck.stage[(size_t)j * ck.n_pixels + (px + py * sc.W)], make_float4(xyz.x, xyz.y, xyz.z, 0.0f));   // CS:107
+  ck.stage[(size_t)j * ck.n_pixels + (px + py * sc.W)] = make_float4(xyz.x, xyz.y, xyz.z, 0.0f);   // CS:107
 }
 
 // the pending NEE contribution of a slot, as the reference would have added it (CS:187 with CS:400 or CS:407)
 __device__ __forceinline__ float4 wf_pending(const WfState& w, uint32_t slot) {
-  const bool occluded = ld_stream1(reinterpret_cast<const float*>(rec_ptr(w, slot, WF_R_S6)) + 3) < 0.0f;   // wf_traverse marks an occluded segment by a negative length
+  const bool occluded = rec_ptr(w, slot, WF_R_S6)->w < 0.0f;   // wf_traverse marks an occluded segment by a negative length
   float4 c = rec_ld(w, slot, WF_R_S7);
   if (occluded) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407: Le = 0, the sum still happens
   return c;
@@ -593,28 +585,16 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
         else if (store_L) { rec_st(w, slot, WF_R_S2, ps.L); flags &= ~WF_FLAG_LZERO; }
       }
     }
-    // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item.  The first ck.n_static items of
-    // the chunk are dealt out statically -- slot s owns s, s + n_slots, s + 2 n_slots, ... -- so taking one of them needs no
-    // atomic (and no round trip to the one address every warp of the grid is adding to); the rest of the chunk is handed
-    // out through the counter, which keeps the slots busy to the end whatever their paths' lengths were.  Which slot renders
-    // an item never shows in the result (the sample is staged by item).
-#if WF_STATIC_WORK
-    if (it == 0) wid = slot - ck.n_slots;   // so that the first candidate below is item `slot`
-#endif
+    // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item: one atomic per warp.  (Dealing a
+    // share of the items to the slots statically, without the atomic, changed nothing: profiles/r01t_static_l2_tri2_variants.txt.)
     for (;;) {
-      bool dyn = need;
-#if WF_STATIC_WORK
-      if (need && wid + ck.n_slots < ck.n_static) { wid += ck.n_slots; dyn = false; }
-#endif
-      if (__ballot_sync(0xffffffffu, need) == 0u) break;
-      const uint32_t mask = __ballot_sync(0xffffffffu, dyn);
-      if (mask != 0u) {   // one atomic per warp
-        uint32_t first = 0;
-        if (lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
-        first = __shfl_sync(0xffffffffu, first, __ffs(mask) - 1);
-        if (dyn) wid = ck.n_static + first + __popc(mask & ((1u << lane) - 1u));
-      }
+      const uint32_t mask = __ballot_sync(0xffffffffu, need);
+      if (mask == 0u) break;
+      uint32_t first = 0;
+      if (lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
+      first = __shfl_sync(0xffffffffu, first, __ffs(mask) - 1);
       if (need) {
+        wid = first + __popc(mask & ((1u << lane) - 1u));
         if (wid >= total_work) {
           need = false;   // the chunk has no work left: this slot retires
         } else {
@@ -672,14 +652,8 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 // next node or triangle changes nothing; one merged fetch phase per trip -- triangle lanes and node lanes load through the
 // same registers and the warp waits once -- is equal on mesh1m and 5 % slower on the 10M soup.)  Arithmetic per node and per triangle is wide_node / wide_tri
 // (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
-#ifndef WF_TRI2
-#define WF_TRI2 0
-#endif
 #ifndef WF_SSTACK
 #define WF_SSTACK 8          // entries of a lane's traversal stack kept in shared memory, the rest in local memory (0 -> 8: wf_traverse -1.5 % on mesh1m, -2.6 % on soup10m; 5 = 8)
-#endif
-#ifndef WF_TRI_PREFETCH
-#define WF_TRI_PREFETCH 0    // after a node step, prefetch.global.L1 the triangles of the group that are tested in later trips
 #endif
 #ifndef WF_REFILL_MIN
 #define WF_REFILL_MIN 8
@@ -771,27 +745,10 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     if (__ballot_sync(0xffffffffu, have) == 0u) break;
     // ---- triangle step: one triangle for every lane that has some left
     bool done = false;
-#if WF_TRI2
-    // two triangles per trip for the lanes that have two left: both fetches are in flight together
-    if (have && T.y != 0u) {
-      const uint32_t k1 = (uint32_t)__ffs(T.y) - 1u;
-      T.y &= T.y - 1u;
-      const bool two = T.y != 0u;
-      const uint32_t k2 = two ? (uint32_t)__ffs(T.y) - 1u : k1;
-      T.y &= T.y - 1u;   // no-op when T.y is already 0
-      const uint32_t s1 = T.x + k1, s2 = T.x + k2;
-      const float4 A0 = ld_tri(&tris[3 * s1 + 0]), A1 = ld_tri(&tris[3 * s1 + 1]), A2 = ld_tri(&tris[3 * s1 + 2]);
-      const float4 B0 = ld_tri(&tris[3 * s2 + 0]), B1 = ld_tri(&tris[3 * s2 + 1]), B2 = ld_tri(&tris[3 * s2 + 2]);
-      if (STATS) ray_tris += two ? 2u : 1u;
-      if (wide_tri_eval<STATS>(A0, A1, A2, s1, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
-      else if (two && wide_tri_eval<STATS>(B0, B1, B2, s2, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
-    }
-#else
     if (have && T.y != 0u) {
       if (STATS) ray_tris++;
       if (wide_tri<STATS>(tris, T, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
     }
-#endif
     // ---- node step, for the lanes whose triangle group is (now) empty: take the nearest unvisited child of the current
     //      node group (or of the group on top of the stack), fetch it and test its 8 child boxes
     if (have && !done && T.y == 0u) {
@@ -804,18 +761,6 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
         if (G.y & CRT_WIDE_HITS) WF_PUSH(G);
         wide_node<STATS>(nodes, node, r, one, t_min, h.t, G, T, st);
         if (STATS) ray_nodes++;
-#if WF_TRI_PREFETCH
-        {   // the first triangle of the group is tested in the next trip, too soon for a prefetch; the others come later
-          uint32_t m = T.y & (T.y - 1u);
-          while (m) {
-            const uint32_t k = (uint32_t)__ffs(m) - 1u;
-            m &= m - 1u;
-            const char* a = reinterpret_cast<const char*>(tris + 3u * (T.x + k));
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(a + 47));
-          }
-        }
-#endif
       }
     }
     // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
@@ -834,7 +779,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     }
     if (done) {
       if (anyhit) {
-        if (h.idx != light_prim) st_stream1(reinterpret_cast<float*>(rec_ptr(w, slot, WF_R_S6)) + 3, -1.0f);   // occluded
+        if (h.idx != light_prim) rec_ptr(w, slot, WF_R_S6)->w = -1.0f;   // occluded
       } else {
         rec_st(w, slot, WF_R_H, make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f));
         if (fix_class && lin_miss && h.idx != CRT_MAX_U32) w.cls[slot] = (uint8_t)0;   // WF_LIVE_CLASS: a triangle turned the miss into a hit
@@ -937,7 +882,7 @@ __global__ void wf_accumulate(const __grid_constant__ DevScene sc, const WfChunk
   const uint32_t pix = px + py * sc.W;
   float4 a = acc[pix];
   for (uint32_t j = 0; j < ck.n_samples; j++) {
-    const float4 v = ld_stream(&ck.stage[(size_t)j * ck.n_pixels + pix]);
+    const float4 v = ck.stage[(size_t)j * ck.n_pixels + pix];
     a.x += v.x; a.y += v.y; a.z += v.z;
   }
   acc[pix] = a;

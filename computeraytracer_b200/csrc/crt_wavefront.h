@@ -45,7 +45,6 @@ struct WfChunk {
   uint32_t s_first;     // frame number of ordinal 0
   uint32_t s_stride;    // frame number step between ordinals (world size under split-spp, else 1)
   uint32_t n_pixels;    // W * H: stride of the staging buffer
-  uint32_t n_static;    // work items [0, n_static) are dealt to the slots statically (slot s: s, s + n_slots, ...); a multiple of n_slots
   float4* stage;        // [n_samples][n_pixels]: XYZ of each finished path, summed in order by wf_accumulate
 };
 

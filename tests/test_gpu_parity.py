@@ -378,17 +378,15 @@ def test_wavefront_pool_and_chunk_size_never_change_results(gpu, oracle, wf_slot
     assert cg == (int(cc[0]), int(cc[1]), int(cc[2]))
 
 
-@pytest.mark.parametrize("routed,static_eighths,defer", [(0, 0, 0), (1, 0, 0), (2, 0, 0), (0, 6, 0), (2, 8, 1), (1, 5, 1), (2, 0, 1)])
+@pytest.mark.parametrize("routed,defer", [(0, 0), (1, 0), (2, 0), (2, 1), (1, 1)])
 @pytest.mark.parametrize("maker,kw", [(scenes.mesh_scene, dict(n_lon=64, n_lat=32)), (scenes.default_scene, {})])
-def test_wavefront_scheduling_forms_never_change_results(gpu, oracle, monkeypatch, maker, kw, routed, static_eighths, defer):
-    """wf_logic's two scheduling switches -- how live slots reach the next iteration (0: one live list; 1: finish and bounce
-    lists filled by wf_logic and wf_traverse; 2: class bytes + wf_partition -- in 1 and 2 a warp's lanes are in one
-    phase, and with `defer` a path that ends in a bounce warp is finished by the next iteration's finish warps) and the
-    static share of the work items (slot s owns items s, s + n_slots, ... without an atomic) -- decide
-    which thread runs which pixel-sample when, nothing else: accumulator, framebuffer and counters stay the oracle's.
-    A small pool forces many rounds per slot, so the static share is really exercised."""
+def test_wavefront_scheduling_forms_never_change_results(gpu, oracle, monkeypatch, maker, kw, routed, defer):
+    """How wf_logic's live slots reach the next iteration (0: one live list; 1: finish and bounce lists filled by wf_logic
+    and wf_traverse; 2: class bytes + wf_partition -- in 1 and 2 a warp's lanes are in one phase, and with `defer` a path
+    that ends in a bounce warp is finished by the next iteration's finish warps) decides which thread runs which
+    pixel-sample when, nothing else: accumulator, framebuffer and counters stay the oracle's.  A small pool forces many
+    rounds per slot."""
     monkeypatch.setenv("CRT_WF_ROUTED", str(routed))
-    monkeypatch.setenv("CRT_WF_STATIC", str(static_eighths))
     monkeypatch.setenv("CRT_WF_DEFER", str(defer))
     ps = maker(96, 64, **kw)
     gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
