@@ -814,6 +814,27 @@ int crt_scene_stats(crt_ctx* ctx, uint64_t* out, size_t n) {
   return CRT_OK;
 }
 
+// Test hook, host only: the BVH builder of the scene-upload module without a device (tests/test_bvh_builder.py).
+CRT_API int crt_host_build_bvh(const void* prims, size_t nbytes, int threads, uint32_t* nodes, size_t node_words, uint32_t* tri_src,
+                               size_t tri_cap, uint64_t* info, float* bounds) {
+  if ((!prims && nbytes) || nbytes % 80 || !info) return CRT_ERR_ARG;
+  const uint8_t* pb = (const uint8_t*)prims;
+  std::vector<uint32_t> tri_pos;
+  for (size_t i = 0; i < nbytes / 80; i++) {
+    uint32_t cat; memcpy(&cat, pb + i * 80, 4);
+    if (cat == 2u) tri_pos.push_back((uint32_t)i);
+  }
+  crt::BvhResult bvh;
+  crt::build_bvh(pb, tri_pos, threads, bvh);
+  info[0] = bvh.n_nodes; info[1] = bvh.tri_src.size(); info[2] = bvh.max_depth; info[3] = 4 * CRT_NODE_STRIDE;
+  if (bounds) { for (int a = 0; a < 3; a++) { bounds[a] = bvh.lo[a]; bounds[3 + a] = bvh.hi[a]; } bounds[6] = bvh.pad; }
+  if (!nodes) return CRT_OK;
+  if (node_words < bvh.nodes.size() || tri_cap < bvh.tri_src.size() || (!tri_src && !bvh.tri_src.empty())) return CRT_ERR_SIZE;
+  if (!bvh.nodes.empty()) memcpy(nodes, bvh.nodes.data(), bvh.nodes.size() * 4);
+  if (!bvh.tri_src.empty()) memcpy(tri_src, bvh.tri_src.data(), bvh.tri_src.size() * 4);
+  return CRT_OK;
+}
+
 // Test hook (not in crt.h's reference mapping): the CUDA build of crt_detmath.h on n inputs.
 CRT_API int crt_test_detmath(crt_ctx* ctx, const float* x, size_t n, float* sn, float* cs, float* ex, float* pw) {
   if (!ctx || !x || !sn || !cs || !ex || !pw) return CRT_ERR_ARG;

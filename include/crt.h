@@ -194,6 +194,15 @@ CRT_API int crt_scene_stats(crt_ctx* ctx, uint64_t* out, size_t n);
 CRT_API int crt_test_detmath(crt_ctx* ctx, const float* x, size_t n, float* sin_out, float* cos_out,
                              float* exp_out, float* pow_out);
 
+/* Test hook, host only (needs no device and no context): the scene-upload module's BVH builder
+ * (csrc/crt_bvh.cpp) on binding-8 bytes.  Call once with nodes == NULL to size the outputs:
+ * info[0] = wide nodes, info[1] = triangles, info[2] = depth of the wide tree, info[3] = 32-bit words
+ * per node (the device layout of csrc/crt_device.cuh, "Wide8").  bounds = lo[3], hi[3] of the padded
+ * root box, then the padding.  tri_src[slot] = position in binding 8 of the triangle at leaf-order
+ * slot `slot`.  The result does not depend on `threads`. */
+CRT_API int crt_host_build_bvh(const void* prims, size_t nbytes, int threads, uint32_t* nodes, size_t node_words,
+                               uint32_t* tri_src, size_t tri_cap, uint64_t* info, float* bounds);
+
 CRT_API const char* crt_last_error(crt_ctx* ctx);
 CRT_API const char* crt_version(void);
 
