@@ -18,7 +18,7 @@
 namespace crt {
 namespace {
 
-constexpr int kBins = 32;
+constexpr int kBinsDefault = 32, kBinsMax = 256;   // SAH bins per axis; tuning override CRT_BVH_BINS (tools/bvh_eval.py)
 constexpr uint32_t kLeafMax = 3;         // a wide node's meta byte holds the leaf's triangle count in 3 unary bits
 constexpr uint32_t kBvh2LeafMax = 1;     // the binary tree is split down to single triangles; the collapse decides the leaves
 constexpr float kNodeCost = 1.0f;        // SAH weights of the collapse (Ylitie et al. 2017, section 4.1); the triangle weight
@@ -48,6 +48,7 @@ struct Builder {
   std::atomic<uint32_t> next{1};
   std::atomic<uint32_t> max_depth{0};
   int par_depth;
+  int kBins = kBinsDefault;
 
   Builder(std::vector<Item>& it, int threads) : items(it), pool(2 * it.size() + 2) {
     par_depth = 0;
@@ -82,7 +83,7 @@ struct Builder {
         const float c0 = cbox.lo[ax], ext = cbox.hi[ax] - cbox.lo[ax];
         if (!(ext > 0.0f)) continue;
         const float scale = (float)kBins / ext;
-        Box bb[kBins]; uint32_t bc[kBins];
+        Box bb[kBinsMax]; uint32_t bc[kBinsMax];
         for (int b = 0; b < kBins; b++) { bb[b].reset(); bc[b] = 0; }
         for (uint32_t i = first; i < first + count; i++) {
           const Item& it = items[i];
@@ -90,7 +91,7 @@ struct Builder {
           b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
           bb[b].grow(it.lo, it.hi); bc[b]++;
         }
-        float right_area[kBins]; uint32_t right_cnt[kBins];
+        float right_area[kBinsMax]; uint32_t right_cnt[kBinsMax];
         Box acc; acc.reset(); uint32_t cnt = 0;
         for (int b = kBins - 1; b > 0; b--) { acc.grow(bb[b]); cnt += bc[b]; right_area[b] = acc.half_area(); right_cnt[b] = cnt; }
         acc.reset(); cnt = 0;
@@ -189,6 +190,7 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
   for (int a = 0; a < 3; a++) { out.lo[a] = scene.lo[a] - pad; out.hi[a] = scene.hi[a] + pad; }
 
   Builder b(items, n_threads < 1 ? 1 : n_threads);
+  if (const char* e = std::getenv("CRT_BVH_BINS")) { const int v = std::atoi(e); if (v >= 4 && v <= kBinsMax) b.kBins = v; }
   b.build(0, 0, (uint32_t)n, 0);
   const std::vector<BNode>& pool = b.pool;
 

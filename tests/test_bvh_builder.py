@@ -221,3 +221,17 @@ def test_argument_errors(lib):
     assert lib.crt_host_build_bvh(raw.ctypes.data, 80, 1, None, 0, None, 0, None, None) == 1
     nodes = np.zeros(4, dtype=np.uint32); src = np.zeros(1, dtype=np.uint32)
     assert lib.crt_host_build_bvh(raw.ctypes.data, 80, 1, nodes.ctypes.data, nodes.size, src.ctypes.data, 1, info.ctypes.data, None) == 3   # CRT_ERR_SIZE
+
+
+@pytest.mark.parametrize("bins", ["8", "128", "256"])
+def test_bin_count_override_builds_a_valid_tree(lib, monkeypatch, bins):
+    """CRT_BVH_BINS (tuning, tools/bvh_eval.py) changes the shape of the tree, never its invariants."""
+    ps = scenes.soup_scene(64, 48, n=20_000)
+    ref = build(lib, ps.primitives)
+    monkeypatch.setenv("CRT_BVH_BINS", bins)
+    nodes, src, depth, bounds = build(lib, ps.primitives)
+    assert check_tree(nodes, src, depth, bounds, ps.primitives)[0] == 20_000
+    assert np.array_equal(bounds, ref[3])
+    monkeypatch.setenv("CRT_BVH_BINS", "32")          # the default, spelled out: the same bytes as with no override
+    again = build(lib, ps.primitives)
+    assert np.array_equal(again[0], ref[0]) and np.array_equal(again[1], ref[1])

@@ -1,0 +1,105 @@
+/* wide8_sim.c -- CPU walk of the Wide8 tree in the order wf_traverse uses (csrc/crt_device.cuh: nearest unvisited child of
+ * the current node group by ray octant, a node's leaf triangles before its inner children, closest-hit shrinking t_max,
+ * any-hit for shadow rays), counting nodes fetched and triangles tested per ray.  A planning tool for the builder
+ * (tools/bvh_eval.py): tree shape changes speed only, so candidate builders are compared here by visit counts before
+ * they get GPU time.  Arithmetic is plain float, not the kernels' bit-exact contract -- counts, not results.
+ *
+ *   gcc -O2 -shared -fPIC -o wide8_sim.so tools/wide8_sim.c -lm
+ */
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#define WORDS 20
+#define HITS 0xFF000000u
+
+typedef struct {
+  uint32_t x, y;
+} u2;
+
+static inline float qf(const uint32_t* w, int word, int i) { return (float)((w[word + (i >> 2)] >> (8 * (i & 3))) & 0xFFu); }
+
+/* rays: n x 8 floats (o.xyz, tmax, d.xyz, any-hit flag); out_t, out_slot: closest hit (slot = -1: none);
+ * counts: n x 2 uint32 (nodes, triangles).  tris: 9 floats per leaf-order slot (v0, e1, e2). */
+void wide8_trace(const uint32_t* nodes, uint32_t n_nodes, const float* tris, const float* rays, uint32_t n, float tmin, float* out_t,
+                 int32_t* out_slot, uint32_t* counts) {
+  for (uint32_t r = 0; r < n; r++) {
+    const float* R = rays + 8 * (size_t)r;
+    const float o[3] = {R[0], R[1], R[2]}, d[3] = {R[4], R[5], R[6]};
+    float tmax = R[3];
+    const int anyhit = R[7] != 0.0f;
+    float id[3];
+    for (int a = 0; a < 3; a++) {
+      float v = 1.0f / d[a];
+      if (v > 1e18f) v = 1e18f;
+      if (v < -1e18f) v = -1e18f;
+      id[a] = v;
+    }
+    const uint32_t oct = (d[0] < 0 ? 1u : 0u) | (d[1] < 0 ? 2u : 0u) | (d[2] < 0 ? 4u : 0u), octinv = 7u ^ oct;
+    uint32_t nn = 0, nt = 0;
+    int32_t best = -1;
+    u2 stack[64];
+    int sp = 0;
+    u2 G = {0u, n_nodes ? 0x80000000u : 0u};   /* the root as the only child of a virtual group */
+    int done = 0;
+    while (!done) {
+      if (!(G.y & HITS)) {
+        if (sp == 0) break;
+        G = stack[--sp];
+      }
+      const uint32_t b = 31u - (uint32_t)__builtin_clz(G.y);   /* nearest unvisited inner child of the group */
+      G.y &= ~(1u << b);
+      const uint32_t slot = (b - 24u) ^ octinv;
+      const uint32_t node = G.x + (uint32_t)__builtin_popcount(G.y & 0xFFu & ((1u << slot) - 1u));
+      if (G.y & HITS) stack[sp++] = G;
+      const uint32_t* w = nodes + (size_t)node * WORDS;
+      nn++;
+      float p[3], st[3];
+      memcpy(p, w, 12);
+      for (int a = 0; a < 3; a++) st[a] = ldexpf(1.0f, (int)((w[3] >> (8 * a)) & 0xFFu) - 127 - 15);
+      const uint32_t imask = w[3] >> 24;
+      uint32_t hit_inner = 0, tri_mask = 0;
+      for (int i = 0; i < 8; i++) {
+        const uint32_t meta = (w[6 + (i >> 2)] >> (8 * (i & 3))) & 0xFFu;
+        if (!meta) continue;
+        float tn = tmin, tf = tmax;
+        for (int a = 0; a < 3; a++) {
+          const float lo = p[a] + qf(w, 8 + 2 * a, i) * st[a], hi = p[a] + qf(w, 14 + 2 * a, i) * st[a];
+          float t0 = (lo - o[a]) * id[a], t1 = (hi - o[a]) * id[a];
+          if (t0 > t1) { const float x = t0; t0 = t1; t1 = x; }
+          if (t0 > tn) tn = t0;
+          if (t1 < tf) tf = t1;
+        }
+        if (!(tn <= tf)) continue;
+        if ((meta >> 5) == 1u && (meta & 31u) >= 24u) hit_inner |= 1u << (24u + ((uint32_t)i ^ octinv));
+        else tri_mask |= (meta >> 5) << (meta & 31u);
+      }
+      G.x = w[4];
+      G.y = hit_inner | imask;
+      while (tri_mask) {   /* the node's triangles first */
+        const uint32_t k = (uint32_t)__builtin_ctz(tri_mask);
+        tri_mask &= tri_mask - 1u;
+        const uint32_t s = w[5] + k;
+        const float* T = tris + 9 * (size_t)s;
+        nt++;
+        const float* e1 = T + 3; const float* e2 = T + 6;
+        const float pv[3] = {d[1] * e2[2] - d[2] * e2[1], d[2] * e2[0] - d[0] * e2[2], d[0] * e2[1] - d[1] * e2[0]};
+        const float det = e1[0] * pv[0] + e1[1] * pv[1] + e1[2] * pv[2];
+        if (!(fabsf(det) >= 1e-8f)) continue;
+        const float inv = 1.0f / det;
+        const float tv[3] = {o[0] - T[0], o[1] - T[1], o[2] - T[2]};
+        const float u = (tv[0] * pv[0] + tv[1] * pv[1] + tv[2] * pv[2]) * inv;
+        if (!(u >= 0.0f && u <= 1.0f)) continue;
+        const float qv[3] = {tv[1] * e1[2] - tv[2] * e1[1], tv[2] * e1[0] - tv[0] * e1[2], tv[0] * e1[1] - tv[1] * e1[0]};
+        const float v = (d[0] * qv[0] + d[1] * qv[1] + d[2] * qv[2]) * inv;
+        if (!(v >= 0.0f && u + v <= 1.0f)) continue;
+        const float t = (e2[0] * qv[0] + e2[1] * qv[1] + e2[2] * qv[2]) * inv;
+        if (!(t >= tmin && t <= tmax)) continue;
+        tmax = t; best = (int32_t)s;
+        if (anyhit) { done = 1; break; }
+      }
+    }
+    out_t[r] = tmax; out_slot[r] = best;
+    counts[2 * (size_t)r] = nn; counts[2 * (size_t)r + 1] = nt;
+  }
+}
