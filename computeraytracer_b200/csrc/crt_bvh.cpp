@@ -194,6 +194,8 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
   b.build(0, 0, (uint32_t)n, 0);
   const std::vector<BNode>& pool = b.pool;
 
+  bool optimal_slots = false;
+  if (const char* e = std::getenv("CRT_BVH_SLOTS")) optimal_slots = std::atoi(e) == 1;
   // ---- which BVH2 subtrees become wide nodes, which become leaves: the SAH-optimal collapse of Ylitie et al. (2017,
   // section 4.1) by dynamic programming.  cost[n][i-1] = cheapest way to represent the subtree of n as at most i
   // children of a wide node (i = 1: one child, either a leaf of <= 3 triangles or a wide node of its own).
@@ -279,6 +281,31 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
         }
       }
       slot_of[bi] = bs; slot_used[bs] = true; child_done[bi] = true;
+    }
+    if (optimal_slots) {
+      // tuning (CRT_BVH_SLOTS=1): the assignment that maximises the summed score exactly, by dynamic programming over the
+      // sets of used slots (child k takes a free slot of a set with k slots used)
+      float score[8][8];
+      for (int i = 0; i < nc; i++) {
+        const Box& cb = pool[ch[i]].box;
+        const float off[3] = {0.5f * (cb.lo[0] + cb.hi[0]) - cen[0], 0.5f * (cb.lo[1] + cb.hi[1]) - cen[1], 0.5f * (cb.lo[2] + cb.hi[2]) - cen[2]};
+        for (int sl = 0; sl < 8; sl++) score[i][sl] = ((sl & 1) ? off[0] : -off[0]) + ((sl & 2) ? off[1] : -off[1]) + ((sl & 4) ? off[2] : -off[2]);
+      }
+      float dp[256]; int8_t from[256];
+      for (int m = 0; m < 256; m++) { dp[m] = -std::numeric_limits<float>::infinity(); from[m] = -1; }
+      dp[0] = 0.0f;
+      for (int m = 0; m < 256; m++) {
+        const int k = __builtin_popcount((unsigned)m);
+        if (k >= nc || dp[m] == -std::numeric_limits<float>::infinity()) continue;
+        for (int sl = 0; sl < 8; sl++) {
+          if (m & (1 << sl)) continue;
+          const float v = dp[m] + score[k][sl];
+          if (v > dp[m | (1 << sl)]) { dp[m | (1 << sl)] = v; from[m | (1 << sl)] = (int8_t)sl; }
+        }
+      }
+      int bm = -1; float bv = -std::numeric_limits<float>::infinity();
+      for (int m = 0; m < 256; m++) if (__builtin_popcount((unsigned)m) == nc && dp[m] > bv) { bv = dp[m]; bm = m; }
+      for (int k = nc - 1, m = bm; k >= 0; k--) { slot_of[k] = from[m]; m &= ~(1 << from[m]); }
     }
     int child_in[8]; for (int sl = 0; sl < 8; sl++) child_in[sl] = -1;
     for (int i = 0; i < nc; i++) child_in[slot_of[i]] = i;

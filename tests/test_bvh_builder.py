@@ -235,3 +235,14 @@ def test_bin_count_override_builds_a_valid_tree(lib, monkeypatch, bins):
     monkeypatch.setenv("CRT_BVH_BINS", "32")          # the default, spelled out: the same bytes as with no override
     again = build(lib, ps.primitives)
     assert np.array_equal(again[0], ref[0]) and np.array_equal(again[1], ref[1])
+
+
+def test_optimal_slot_assignment_builds_a_valid_tree(lib, monkeypatch):
+    """CRT_BVH_SLOTS=1 (tuning) only permutes the children of a node among its 8 slots."""
+    ps = scenes.mesh_scene(64, 48, n_lon=96, n_lat=48)
+    ref = build(lib, ps.primitives)
+    monkeypatch.setenv("CRT_BVH_SLOTS", "1")
+    nodes, src, depth, bounds = build(lib, ps.primitives)
+    assert check_tree(nodes, src, depth, bounds, ps.primitives)[0] == 2 * 96 * 48
+    assert nodes.shape == ref[0].shape and depth == ref[2]          # same nodes, children (and leaf order) permuted
+    assert not np.array_equal(nodes, ref[0])

@@ -7,6 +7,7 @@ changes results (DESIGN.md "Conservative culling"), only these counts, which is 
 On mesh1m it gives 8.4 nodes / 2.6 triangles per queued ray where the device counters say 9.4 / 3.1.
 
     python tools/bvh_eval.py [mesh|soup] [n_lon or n_triangles] [ENV=VALUE ...]      e.g.  CRT_BVH_BINS=128
+    SIM_ORDER=1 python tools/bvh_eval.py ...     children visited by entry distance instead of by ray octant
 """
 import ctypes as C
 import os
@@ -23,6 +24,7 @@ from computeraytracer_b200 import scenes  # noqa: E402
 from computeraytracer_b200.build import build_libcrt  # noqa: E402
 
 ROOM = 555.0
+ORDER = int(os.environ.get("SIM_ORDER", "0"))   # 1: children by entry distance with culling on the way back (bound for any child ordering)
 TMIN = 1e-3
 
 
@@ -32,7 +34,7 @@ def load_sim():
     if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
         subprocess.run(["gcc", "-O2", "-shared", "-fPIC", "-o", so, src, "-lm"], check=True)
     lib = C.CDLL(so)
-    lib.wide8_trace.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.wide8_trace.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
     lib.wide8_trace.restype = None
     return lib
 
@@ -96,7 +98,7 @@ def main():
         rays = np.zeros((o.shape[0], 8), dtype=np.float32)
         rays[:, 0:3] = o; rays[:, 3] = tmax; rays[:, 4:7] = d; rays[:, 7] = 1.0 if anyhit else 0.0
         t = np.zeros(o.shape[0], dtype=np.float32); slot = np.zeros(o.shape[0], dtype=np.int32); cnt = np.zeros((o.shape[0], 2), dtype=np.uint32)
-        sim.wide8_trace(nodes.ctypes.data, int(info[0]), tri.ctypes.data, rays.ctypes.data, o.shape[0], TMIN, t.ctypes.data, slot.ctypes.data, cnt.ctypes.data)
+        sim.wide8_trace(nodes.ctypes.data, int(info[0]), tri.ctypes.data, rays.ctypes.data, o.shape[0], TMIN, t.ctypes.data, slot.ctypes.data, cnt.ctypes.data, ORDER)
         return o, d, t, slot, cnt, keep
 
     # primary rays: every 6th pixel in x and y (camera_ray, CS:470-500, pixel centres)
