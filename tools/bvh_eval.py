@@ -36,6 +36,8 @@ def load_sim():
     lib = C.CDLL(so)
     lib.wide8_trace.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
     lib.wide8_trace.restype = None
+    lib.wide8_warp_sim.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.wide8_warp_sim.restype = None
     return lib
 
 
@@ -92,11 +94,14 @@ def main():
     sim = load_sim()
     rng = np.random.default_rng(7)
 
+    queued = {False: [], True: []}   # the rays as the kernel's queues hold them: extension rays, shadow rays
+
     def trace(o, d, tmax, anyhit):
         keep = slab(o, d, bounds[0:3], bounds[3:6], tmax)[0] & (tmax > 0)   # hits_root_box: the others are never queued
         o, d, tmax = o[keep], d[keep], tmax[keep]
         rays = np.zeros((o.shape[0], 8), dtype=np.float32)
         rays[:, 0:3] = o; rays[:, 3] = tmax; rays[:, 4:7] = d; rays[:, 7] = 1.0 if anyhit else 0.0
+        queued[anyhit].append(rays)
         t = np.zeros(o.shape[0], dtype=np.float32); slot = np.zeros(o.shape[0], dtype=np.int32); cnt = np.zeros((o.shape[0], 2), dtype=np.uint32)
         sim.wide8_trace(nodes.ctypes.data, int(info[0]), tri.ctypes.data, rays.ctypes.data, o.shape[0], TMIN, t.ctypes.data, slot.ctypes.data, cnt.ctypes.data, ORDER)
         return o, d, t, slot, cnt, keep
@@ -156,6 +161,17 @@ def main():
             print(f"{name:<28}{n_all:>9}{n_q:>9}{cnt[:, 0].mean():>14.2f}{cnt[:, 1].mean():>13.2f}{int(cnt[:, 0].max()):>11}")
             tot_n += int(cnt[:, 0].sum()); tot_t += int(cnt[:, 1].sum()); tot_r += n_q
     print(f"{'all queued rays':<28}{'':>9}{tot_r:>9}{tot_n / tot_r:>14.2f}{tot_t / tot_r:>13.2f}   80 B x nodes + 48 B x tris = {(80 * tot_n + 48 * tot_t) / tot_r:.0f} B/ray")
+    if os.environ.get("SIM_WARP"):
+        # warp-level model of wf_traverse's schedule (wide8_sim.c): steps and lanes per step; ~265 instructions per node
+        # step and ~80 per triangle step on the GPU
+        allrays = np.ascontiguousarray(np.concatenate(queued[False] + queued[True]))
+        print(f"{'schedule':<44}{'node steps/ray':>15}{'lanes':>7}{'tri steps/ray':>15}{'lanes':>7}{'nodes/ray':>11}{'tris/ray':>10}{'instr/ray':>11}")
+        for name, mode, tri_min in [("kernel (1 triangle, then 1 node per trip)", 0, 1)] + [(f"postponed leaves, triangle step at >= {k} lanes", 1, k) for k in (2, 4, 8, 12, 16, 24)]:
+            out = np.zeros(6, dtype=np.uint64)
+            sim.wide8_warp_sim(nodes.ctypes.data, int(info[0]), tri.ctypes.data, allrays.ctypes.data, allrays.shape[0], TMIN, mode, 8, tri_min, out.ctypes.data)
+            ns, nl, ts, tl, nv, tv = (float(x) for x in out)
+            nr = allrays.shape[0]
+            print(f"{name:<44}{ns / nr:>15.3f}{nl / max(ns, 1):>7.1f}{ts / nr:>15.3f}{tl / max(ts, 1):>7.1f}{nv / nr:>11.2f}{tv / nr:>10.2f}{(265 * ns + 80 * ts) / nr:>11.1f}")
 
 
 if __name__ == "__main__":

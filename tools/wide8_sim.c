@@ -202,3 +202,138 @@ static void trace_sorted(const uint32_t* nodes, uint32_t n_nodes, const float* t
     counts[2 * (size_t)r] = nn; counts[2 * (size_t)r + 1] = nt;
   }
 }
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Warp-level model of wf_traverse's loop: 32 lanes, each owning one ray at a time, refilled from the queue when at least
+ * `refill_min` lanes are idle (or none has a ray).  A trip is a triangle step (one triangle for every lane that has some
+ * pending) followed by a node step (for the lanes whose triangle group is empty by then).  Counts warp-level steps and
+ * the lanes active in them -- the kernel is issue-bound at about 265 instructions per node step and 80 per triangle
+ * step, so steps x instructions per queued ray is what a scheduling variant has to lower.
+ *   mode 0: the kernel's schedule.
+ *   mode 1: a lane keeps stepping through nodes while it holds one postponed triangle group; the triangle step runs only
+ *           when at least `tri_min` lanes hold triangles, or a lane holds a group and has just found a second one, or no
+ *           lane has node work (postponed triangles are tested without the closer hit they might have provided, so some
+ *           extra nodes are visited).
+ * out[0..5] = node steps, lanes in node steps, triangle steps, lanes in triangle steps, nodes visited, triangles tested. */
+typedef struct {
+  int have, anyhit;
+  float o[3], d[3], id[3], tmax;
+  uint32_t octinv;
+  u2 G, stack[64];
+  int sp;
+  uint32_t T_base, T_mask;      /* pending triangle group */
+  uint32_t P_base, P_mask;      /* postponed triangle group (mode 1) */
+  int finished_nodes;           /* traversal has no node left; only triangles remain */
+} Lane;
+
+static void lane_start(Lane* L, const float* R, uint32_t n_nodes) {
+  L->have = 1; L->anyhit = R[7] != 0.0f;
+  for (int a = 0; a < 3; a++) {
+    L->o[a] = R[a]; L->d[a] = R[4 + a];
+    float v = 1.0f / L->d[a]; if (v > 1e18f) v = 1e18f; if (v < -1e18f) v = -1e18f; L->id[a] = v;
+  }
+  L->tmax = R[3];
+  L->octinv = 7u ^ ((L->d[0] < 0 ? 1u : 0u) | (L->d[1] < 0 ? 2u : 0u) | (L->d[2] < 0 ? 4u : 0u));
+  L->G.x = 0; L->G.y = n_nodes ? 0x80000000u : 0u;
+  L->sp = 0; L->T_mask = L->P_mask = 0; L->finished_nodes = 0;
+}
+
+/* one node step; returns 0 when there was no node left */
+static int lane_node(Lane* L, const uint32_t* nodes, float tmin) {
+  if (!(L->G.y & HITS)) {
+    if (L->sp == 0) { L->finished_nodes = 1; return 0; }
+    L->G = L->stack[--L->sp];
+  }
+  const uint32_t b = 31u - (uint32_t)__builtin_clz(L->G.y);
+  L->G.y &= ~(1u << b);
+  const uint32_t slot = (b - 24u) ^ L->octinv;
+  const uint32_t node = L->G.x + (uint32_t)__builtin_popcount(L->G.y & 0xFFu & ((1u << slot) - 1u));
+  if (L->G.y & HITS) L->stack[L->sp++] = L->G;
+  const uint32_t* w = nodes + (size_t)node * WORDS;
+  float p[3], st[3];
+  memcpy(p, w, 12);
+  for (int a = 0; a < 3; a++) st[a] = ldexpf(1.0f, (int)((w[3] >> (8 * a)) & 0xFFu) - 127 - 15);
+  uint32_t hit_inner = 0, tri_mask = 0;
+  for (int i = 0; i < 8; i++) {
+    const uint32_t meta = (w[6 + (i >> 2)] >> (8 * (i & 3))) & 0xFFu;
+    if (!meta) continue;
+    float tn = tmin, tf = L->tmax;
+    for (int a = 0; a < 3; a++) {
+      const float lo = p[a] + qf(w, 8 + 2 * a, i) * st[a], hi = p[a] + qf(w, 14 + 2 * a, i) * st[a];
+      float t0 = (lo - L->o[a]) * L->id[a], t1 = (hi - L->o[a]) * L->id[a];
+      if (t0 > t1) { const float x = t0; t0 = t1; t1 = x; }
+      if (t0 > tn) tn = t0;
+      if (t1 < tf) tf = t1;
+    }
+    if (!(tn <= tf)) continue;
+    if ((meta >> 5) == 1u && (meta & 31u) >= 24u) hit_inner |= 1u << (24u + ((uint32_t)i ^ L->octinv));
+    else tri_mask |= (meta >> 5) << (meta & 31u);
+  }
+  L->G.x = w[4]; L->G.y = hit_inner | (w[3] >> 24);
+  L->T_base = w[5]; L->T_mask = tri_mask;
+  return 1;
+}
+
+/* one triangle of the pending group (the postponed one first); returns 1 when an any-hit ray found its occluder */
+static int lane_tri(Lane* L, const float* tris, float tmin) {
+  uint32_t* mask = L->P_mask ? &L->P_mask : &L->T_mask;
+  const uint32_t base = L->P_mask ? L->P_base : L->T_base;
+  const uint32_t k = (uint32_t)__builtin_ctz(*mask);
+  *mask &= *mask - 1u;
+  float t;
+  if (tri_test(tris + 9 * (size_t)(base + k), L->o, L->d, tmin, L->tmax, &t)) { L->tmax = t; return L->anyhit; }
+  return 0;
+}
+
+void wide8_warp_sim(const uint32_t* nodes, uint32_t n_nodes, const float* tris, const float* rays, uint32_t n, float tmin, int mode,
+                    int refill_min, int tri_min, uint64_t* out) {
+  static Lane lane[32];
+  for (int l = 0; l < 32; l++) lane[l].have = 0;
+  for (int k = 0; k < 6; k++) out[k] = 0;
+  uint32_t next = 0;
+  for (;;) {
+    int idle = 0, busy = 0;
+    for (int l = 0; l < 32; l++) { if (lane[l].have) busy++; else idle++; }
+    if (next < n && (idle >= refill_min || busy == 0))
+      for (int l = 0; l < 32 && next < n; l++) if (!lane[l].have) lane_start(&lane[l], rays + 8 * (size_t)next++, n_nodes);
+    busy = 0;
+    for (int l = 0; l < 32; l++) busy += lane[l].have;
+    if (!busy) break;
+    /* ---- triangle step */
+    int want = 0, must = 0, node_work = 0;
+    for (int l = 0; l < 32; l++) {
+      Lane* L = &lane[l];
+      if (!L->have) continue;
+      const int tri = (L->T_mask | L->P_mask) != 0;
+      want += tri;
+      if (mode == 0) continue;
+      if ((L->P_mask && L->T_mask) || (tri && L->finished_nodes)) must = 1;
+      if (!L->finished_nodes && !(L->P_mask && L->T_mask)) node_work++;
+    }
+    const int run_tri = mode == 0 ? want > 0 : (want > 0 && (want >= tri_min || must || node_work == 0));
+    if (run_tri) {
+      out[2]++;
+      for (int l = 0; l < 32; l++) {
+        Lane* L = &lane[l];
+        if (!L->have || !(L->T_mask | L->P_mask)) continue;
+        out[3]++; out[5]++;
+        if (lane_tri(L, tris, tmin)) L->have = 0;
+      }
+    }
+    /* ---- node step */
+    int stepped = 0;
+    for (int l = 0; l < 32; l++) {
+      Lane* L = &lane[l];
+      if (!L->have) continue;
+      if (mode == 0) { if (L->T_mask) continue; }
+      else {
+        if (L->P_mask && L->T_mask) continue;              /* two groups pending: wait for the triangle step */
+        if (L->T_mask) { L->P_base = L->T_base; L->P_mask = L->T_mask; L->T_mask = 0; }   /* postpone, keep walking */
+        if (L->finished_nodes) { if (!L->P_mask) L->have = 0; continue; }
+      }
+      if (lane_node(L, nodes, tmin)) { stepped++; out[4]++; }
+      else if (!(L->T_mask | L->P_mask)) L->have = 0;       /* no node left and no triangle pending: the ray is done */
+    }
+    if (stepped) { out[0]++; out[1] += (uint64_t)stepped; }
+  }
+}
