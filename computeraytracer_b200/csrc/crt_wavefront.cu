@@ -655,6 +655,9 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 #ifndef WF_SSTACK
 #define WF_SSTACK 8          // entries of a lane's traversal stack kept in shared memory, the rest in local memory (0 -> 8: wf_traverse -1.5 % on mesh1m, -2.6 % on soup10m; 5 = 8)
 #endif
+#ifndef WF_POSTPONE
+#define WF_POSTPONE 0        // > 0: postponed leaves, the triangle step waits for this many lanes (see wf_traverse)
+#endif
 #ifndef WF_REFILL_MIN
 #define WF_REFILL_MIN 8
 #endif
@@ -688,6 +691,11 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
   uint2 stack[CRT_BVH_STACK];
 #define WF_PUSH(g) do { stack[sp++] = (g); } while (0)
 #define WF_POP(g) do { (g) = stack[--sp]; } while (0)
+#endif
+#if WF_POSTPONE
+  __shared__ uint2 s_post[WF_BLOCK];   // a lane's postponed triangle group
+  bool walked = false;                 // the lane's ray has no node left to visit
+  s_post[threadIdx.x] = make_uint2(0u, 0u);
 #endif
   int sp = 0;
   uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);   // node group and triangle group of the lane's ray (crt_device.cuh)
@@ -738,6 +746,9 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
           T = make_uint2(0u, 0u);
           sp = 0;
           have = true;
+#if WF_POSTPONE
+          s_post[threadIdx.x] = make_uint2(0u, 0u); walked = !r.valid;
+#endif
           ray_nodes = ray_tris = 0;
         }
       }
@@ -745,6 +756,45 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     if (__ballot_sync(0xffffffffu, have) == 0u) break;
     // ---- triangle step: one triangle for every lane that has some left
     bool done = false;
+#if WF_POSTPONE
+    // Postponed leaves (tuning, off by default; modelled in tools/wide8_sim.c: node steps 22 -> 25 lanes, 7-9 % fewer
+    // step instructions per ray): a lane keeps walking nodes while it holds ONE postponed triangle group, and the
+    // triangle step runs only when WF_POSTPONE lanes hold triangles, or a lane has found a second group, or a lane has
+    // triangles left and no node, or nobody has node work.  Every triangle of a hit leaf is still tested against the
+    // best hit known at that moment, so results are the same; postponed triangles cannot shorten the ray in time, so a
+    // few more nodes are visited.
+    {
+      uint2 P = s_post[threadIdx.x];   // the postponed group (y == 0: none)
+      const bool both = P.y != 0u && T.y != 0u;
+      const bool tri_have = have && (T.y | P.y) != 0u;
+      const uint32_t want = (uint32_t)__popc(__ballot_sync(0xffffffffu, tri_have));
+      const bool run_tri = want != 0u && (want >= WF_POSTPONE || __ballot_sync(0xffffffffu, have && (both || (tri_have && walked))) != 0u ||
+                                          __ballot_sync(0xffffffffu, have && !walked && !both) == 0u);
+      if (run_tri && tri_have) {
+        const bool from_p = P.y != 0u;
+        uint2 S = from_p ? P : T;
+        if (STATS) ray_tris++;
+        if (wide_tri<STATS>(tris, S, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
+        if (from_p) P = S; else T = S;
+      }
+      if (have && !done && !(P.y != 0u && T.y != 0u)) {
+        if (T.y != 0u) { P = T; T.y = 0u; }
+        if (!walked && !(G.y & CRT_WIDE_HITS)) {
+          if (sp == 0) walked = true;
+          else WF_POP(G);
+        }
+        if (!walked) {
+          const uint32_t node = wide_pop_child(G, r.octinv);
+          if (G.y & CRT_WIDE_HITS) WF_PUSH(G);
+          wide_node<STATS>(nodes, node, r, one, t_min, h.t, G, T, st);
+          if (STATS) ray_nodes++;
+        } else if (P.y == 0u) {
+          done = true;   // no node and no triangle left
+        }
+      }
+      s_post[threadIdx.x] = P;
+    }
+#else
     if (have && T.y != 0u) {
       if (STATS) ray_tris++;
       if (wide_tri<STATS>(tris, T, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
@@ -763,6 +813,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
         if (STATS) ray_nodes++;
       }
     }
+#endif
     // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
     //      to the next iteration's shade queue (surface) or finish queue (miss)
     const bool fin_ext = done && !anyhit;
