@@ -36,7 +36,7 @@ def load_sim():
     lib = C.CDLL(so)
     lib.wide8_trace.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
     lib.wide8_trace.restype = None
-    lib.wide8_warp_sim.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.wide8_warp_sim.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
     lib.wide8_warp_sim.restype = None
     return lib
 
@@ -166,9 +166,11 @@ def main():
         # step and ~80 per triangle step on the GPU
         allrays = np.ascontiguousarray(np.concatenate(queued[False] + queued[True]))
         print(f"{'schedule':<44}{'node steps/ray':>15}{'lanes':>7}{'tri steps/ray':>15}{'lanes':>7}{'nodes/ray':>11}{'tris/ray':>10}{'instr/ray':>11}")
-        for name, mode, tri_min in [("kernel (1 triangle, then 1 node per trip)", 0, 1)] + [(f"postponed leaves, triangle step at >= {k} lanes", 1, k) for k in (2, 4, 8, 12, 16, 24)]:
+        rows = [("kernel (1 triangle, then 1 node per trip)", 0, 1, 1)] + [(f"postponed leaves, triangle step at >= {k} lanes", 1, k, 1) for k in (2, 4, 8, 12, 16, 24)]
+        rows += [(f"up to {dq} postponed groups, >= {k} lanes", 1, k, dq) for dq in (2, 4) for k in (8, 16, 24)]
+        for name, mode, tri_min, dq in rows:
             out = np.zeros(6, dtype=np.uint64)
-            sim.wide8_warp_sim(nodes.ctypes.data, int(info[0]), tri.ctypes.data, allrays.ctypes.data, allrays.shape[0], TMIN, mode, 8, tri_min, out.ctypes.data)
+            sim.wide8_warp_sim(nodes.ctypes.data, int(info[0]), tri.ctypes.data, allrays.ctypes.data, allrays.shape[0], TMIN, mode, int(os.environ.get("SIM_REFILL", "8")), tri_min, dq, out.ctypes.data)
             ns, nl, ts, tl, nv, tv = (float(x) for x in out)
             nr = allrays.shape[0]
             print(f"{name:<44}{ns / nr:>15.3f}{nl / max(ns, 1):>7.1f}{ts / nr:>15.3f}{tl / max(ts, 1):>7.1f}{nv / nr:>11.2f}{tv / nr:>10.2f}{(265 * ns + 80 * ts) / nr:>11.1f}")

@@ -222,7 +222,8 @@ typedef struct {
   u2 G, stack[64];
   int sp;
   uint32_t T_base, T_mask;      /* pending triangle group */
-  uint32_t P_base, P_mask;      /* postponed triangle group (mode 1) */
+  uint32_t P_base, P_mask;      /* postponed triangle group being tested (mode 1) */
+  uint32_t Q_base[8], Q_mask[8]; int nq;   /* further postponed groups (mode 1 with depth > 1) */
   int finished_nodes;           /* traversal has no node left; only triangles remain */
 } Lane;
 
@@ -235,7 +236,7 @@ static void lane_start(Lane* L, const float* R, uint32_t n_nodes) {
   L->tmax = R[3];
   L->octinv = 7u ^ ((L->d[0] < 0 ? 1u : 0u) | (L->d[1] < 0 ? 2u : 0u) | (L->d[2] < 0 ? 4u : 0u));
   L->G.x = 0; L->G.y = n_nodes ? 0x80000000u : 0u;
-  L->sp = 0; L->T_mask = L->P_mask = 0; L->finished_nodes = 0;
+  L->sp = 0; L->T_mask = L->P_mask = 0; L->finished_nodes = 0; L->nq = 0;
 }
 
 /* one node step; returns 0 when there was no node left */
@@ -281,12 +282,15 @@ static int lane_tri(Lane* L, const float* tris, float tmin) {
   const uint32_t k = (uint32_t)__builtin_ctz(*mask);
   *mask &= *mask - 1u;
   float t;
-  if (tri_test(tris + 9 * (size_t)(base + k), L->o, L->d, tmin, L->tmax, &t)) { L->tmax = t; return L->anyhit; }
-  return 0;
+  const int hit = tri_test(tris + 9 * (size_t)(base + k), L->o, L->d, tmin, L->tmax, &t);
+  if (hit) L->tmax = t;
+  if (!L->P_mask && L->nq) { L->nq--; L->P_base = L->Q_base[L->nq]; L->P_mask = L->Q_mask[L->nq]; }   /* next postponed group */
+  return hit && L->anyhit;
 }
 
 void wide8_warp_sim(const uint32_t* nodes, uint32_t n_nodes, const float* tris, const float* rays, uint32_t n, float tmin, int mode,
-                    int refill_min, int tri_min, uint64_t* out) {
+                    int refill_min, int tri_min, int depth, uint64_t* out) {
+  /* depth: postponed groups a lane may hold (mode 1); it must stop walking when it holds `depth` and finds another */
   static Lane lane[32];
   for (int l = 0; l < 32; l++) lane[l].have = 0;
   for (int k = 0; k < 6; k++) out[k] = 0;
@@ -307,8 +311,9 @@ void wide8_warp_sim(const uint32_t* nodes, uint32_t n_nodes, const float* tris, 
       const int tri = (L->T_mask | L->P_mask) != 0;
       want += tri;
       if (mode == 0) continue;
-      if ((L->P_mask && L->T_mask) || (tri && L->finished_nodes)) must = 1;
-      if (!L->finished_nodes && !(L->P_mask && L->T_mask)) node_work++;
+      const int full = L->P_mask && L->T_mask && L->nq >= depth - 1;
+      if (full || (tri && L->finished_nodes)) must = 1;
+      if (!L->finished_nodes && !full) node_work++;
     }
     const int run_tri = mode == 0 ? want > 0 : (want > 0 && (want >= tri_min || must || node_work == 0));
     if (run_tri) {
@@ -327,8 +332,12 @@ void wide8_warp_sim(const uint32_t* nodes, uint32_t n_nodes, const float* tris, 
       if (!L->have) continue;
       if (mode == 0) { if (L->T_mask) continue; }
       else {
-        if (L->P_mask && L->T_mask) continue;              /* two groups pending: wait for the triangle step */
-        if (L->T_mask) { L->P_base = L->T_base; L->P_mask = L->T_mask; L->T_mask = 0; }   /* postpone, keep walking */
+        if (L->P_mask && L->T_mask && L->nq >= depth - 1) continue;   /* no room to postpone another group: wait for the triangle step */
+        if (L->T_mask) {                                   /* postpone, keep walking */
+          if (!L->P_mask) { L->P_base = L->T_base; L->P_mask = L->T_mask; }
+          else { L->Q_base[L->nq] = L->T_base; L->Q_mask[L->nq] = L->T_mask; L->nq++; }
+          L->T_mask = 0;
+        }
         if (L->finished_nodes) { if (!L->P_mask) L->have = 0; continue; }
       }
       if (lane_node(L, nodes, tmin)) { stepped++; out[4]++; }
