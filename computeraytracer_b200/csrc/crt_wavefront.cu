@@ -655,6 +655,9 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 #ifndef WF_SSTACK
 #define WF_SSTACK 8          // entries of a lane's traversal stack kept in shared memory, the rest in local memory (0 -> 8: wf_traverse -1.5 % on mesh1m, -2.6 % on soup10m; 5 = 8)
 #endif
+#ifndef WF_BATCH_FETCH
+#define WF_BATCH_FETCH 0     // > 0: a warp takes this many BVH-queue entries per atomic (see wf_traverse's refill)
+#endif
 #ifndef WF_POSTPONE
 #define WF_POSTPONE 0        // > 0: postponed leaves, the triangle step waits for this many lanes (see wf_traverse)
 #endif
@@ -700,6 +703,9 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
   int sp = 0;
   uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);   // node group and triangle group of the lane's ray (crt_device.cuh)
   bool have = false, exhausted = false, anyhit = false, lin_miss = false;
+#if WF_BATCH_FETCH
+  uint32_t qnext = 0, qend = 0;   // the warp's current share of the queue (warp-uniform)
+#endif
   uint32_t slot = 0, exclude = CRT_MAX_U32, light_prim = 0;
   V3 d = v3(0.0f, 0.0f, 1.0f);
   WideRay r = wide_ray(v3(0.0f, 0.0f, 0.0f), d);
@@ -714,15 +720,37 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     uint32_t mask = __ballot_sync(0xffffffffu, need);
     if (__popc(mask) < WF_REFILL_MIN && __ballot_sync(0xffffffffu, have) != 0u) mask = 0u;
     if (mask) {
+#if WF_BATCH_FETCH
+      // Batched fetch (tuning, off by default): the warp takes WF_BATCH_FETCH queue entries with one atomic and hands them
+      // to its lanes as they fall idle, so a refill is an index computation plus the new rays' loads and the threshold
+      // WF_REFILL_MIN can come down (tools/wide8_sim.c prices today's refill event at ~90 step-instructions).
+      if (qnext >= qend) {   // warp-uniform: the warp's share is used up
+        uint32_t b0 = 0;
+        if (lane == 0) b0 = atomicAdd(fetch, (uint32_t)WF_BATCH_FETCH);
+        b0 = __shfl_sync(0xffffffffu, b0, 0);
+        qnext = b0 < n ? b0 : n;
+        qend = b0 + (uint32_t)WF_BATCH_FETCH < n ? b0 + (uint32_t)WF_BATCH_FETCH : n;
+      }
+      const uint32_t base = qnext;
+      const uint32_t q_end = qend;
+      qnext = base + (uint32_t)__popc(mask) < qend ? base + (uint32_t)__popc(mask) : qend;
+#else
       uint32_t base = 0;
       const uint32_t leader = __ffs(mask) - 1u;
       if (lane == leader) base = atomicAdd(fetch, (uint32_t)__popc(mask));
       base = __shfl_sync(0xffffffffu, base, leader);
+#endif
       if (need) {
         const uint32_t q = base + __popc(mask & ((1u << lane) - 1u));
+#if WF_BATCH_FETCH
+        if (q >= q_end) {
+          if (q_end == n) exhausted = true;   // the queue itself is used up; otherwise the lane waits for the warp's next batch
+        } else {
+#else
         if (q >= n) {
           exhausted = true;
         } else {
+#endif
           anyhit = q >= n_ext;
           slot = anyhit ? w.shadow_list[q - n_ext] : queue[q];
           const float4 a = rec_ld(w, slot, WF_R_S0);
@@ -753,7 +781,14 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
         }
       }
     }
+#if WF_BATCH_FETCH
+    if (__ballot_sync(0xffffffffu, have) == 0u) {
+      if (__ballot_sync(0xffffffffu, !exhausted) == 0u) break;
+      continue;   // lanes wait for the warp's next batch
+    }
+#else
     if (__ballot_sync(0xffffffffu, have) == 0u) break;
+#endif
     // ---- triangle step: one triangle for every lane that has some left
     bool done = false;
 #if WF_POSTPONE
