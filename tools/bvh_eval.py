@@ -36,7 +36,7 @@ def load_sim():
     lib = C.CDLL(so)
     lib.wide8_trace.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
     lib.wide8_trace.restype = None
-    lib.wide8_warp_sim.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.wide8_warp_sim.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.wide8_warp_sim.restype = None
     return lib
 
@@ -168,9 +168,16 @@ def main():
         print(f"{'schedule':<44}{'node steps/ray':>15}{'lanes':>7}{'tri steps/ray':>15}{'lanes':>7}{'nodes/ray':>11}{'tris/ray':>10}{'instr/ray':>11}")
         rows = [("kernel (1 triangle, then 1 node per trip)", 0, 1, 1)] + [(f"postponed leaves, triangle step at >= {k} lanes", 1, k, 1) for k in (2, 4, 8, 12, 16, 24)]
         rows += [(f"up to {dq} postponed groups, >= {k} lanes", 1, k, dq) for dq in (2, 4) for k in (8, 16, 24)]
+        ref_res = None
         for name, mode, tri_min, dq in rows:
             out = np.zeros(6, dtype=np.uint64)
-            sim.wide8_warp_sim(nodes.ctypes.data, int(info[0]), tri.ctypes.data, allrays.ctypes.data, allrays.shape[0], TMIN, mode, int(os.environ.get("SIM_REFILL", "8")), tri_min, dq, out.ctypes.data)
+            res_t = np.zeros(allrays.shape[0], dtype=np.float32); res_hit = np.zeros(allrays.shape[0], dtype=np.int32)
+            sim.wide8_warp_sim(nodes.ctypes.data, int(info[0]), tri.ctypes.data, allrays.ctypes.data, allrays.shape[0], TMIN, mode, int(os.environ.get("SIM_REFILL", "8")), tri_min, dq, out.ctypes.data, res_t.ctypes.data, res_hit.ctypes.data)
+            if ref_res is None:
+                ref_res = (res_t.copy(), res_hit.copy())
+            else:   # a schedule may change the work, never the answers: closest t of extension rays, occluded or not for shadow rays
+                ext = allrays[:, 7] == 0
+                assert np.array_equal(res_t[ext], ref_res[0][ext]) and np.array_equal(res_hit, ref_res[1]), name
             ns, nl, ts, tl, nv, tv = (float(x) for x in out)
             nr = allrays.shape[0]
             print(f"{name:<44}{ns / nr:>15.3f}{nl / max(ns, 1):>7.1f}{ts / nr:>15.3f}{tl / max(ts, 1):>7.1f}{nv / nr:>11.2f}{tv / nr:>10.2f}{(265 * ns + 80 * ts) / nr:>11.1f}")

@@ -225,6 +225,7 @@ typedef struct {
   uint32_t P_base, P_mask;      /* postponed triangle group being tested (mode 1) */
   uint32_t Q_base[8], Q_mask[8]; int nq;   /* further postponed groups (mode 1 with depth > 1) */
   int finished_nodes;           /* traversal has no node left; only triangles remain */
+  uint32_t idx; int hit;        /* position in the queue; some triangle was accepted */
 } Lane;
 
 static void lane_start(Lane* L, const float* R, uint32_t n_nodes) {
@@ -236,7 +237,7 @@ static void lane_start(Lane* L, const float* R, uint32_t n_nodes) {
   L->tmax = R[3];
   L->octinv = 7u ^ ((L->d[0] < 0 ? 1u : 0u) | (L->d[1] < 0 ? 2u : 0u) | (L->d[2] < 0 ? 4u : 0u));
   L->G.x = 0; L->G.y = n_nodes ? 0x80000000u : 0u;
-  L->sp = 0; L->T_mask = L->P_mask = 0; L->finished_nodes = 0; L->nq = 0;
+  L->sp = 0; L->T_mask = L->P_mask = 0; L->finished_nodes = 0; L->nq = 0; L->hit = 0;
 }
 
 /* one node step; returns 0 when there was no node left */
@@ -283,13 +284,14 @@ static int lane_tri(Lane* L, const float* tris, float tmin) {
   *mask &= *mask - 1u;
   float t;
   const int hit = tri_test(tris + 9 * (size_t)(base + k), L->o, L->d, tmin, L->tmax, &t);
-  if (hit) L->tmax = t;
+  if (hit) { L->tmax = t; L->hit = 1; }
   if (!L->P_mask && L->nq) { L->nq--; L->P_base = L->Q_base[L->nq]; L->P_mask = L->Q_mask[L->nq]; }   /* next postponed group */
   return hit && L->anyhit;
 }
 
 void wide8_warp_sim(const uint32_t* nodes, uint32_t n_nodes, const float* tris, const float* rays, uint32_t n, float tmin, int mode,
-                    int refill_min, int tri_min, int depth, uint64_t* out) {
+                    int refill_min, int tri_min, int depth, uint64_t* out, float* res_t, int32_t* res_hit) {
+#define LANE_DONE(L) do { (L)->have = 0; if (res_t) { res_t[(L)->idx] = (L)->tmax; res_hit[(L)->idx] = (L)->hit; } } while (0)
   /* depth: postponed groups a lane may hold (mode 1); it must stop walking when it holds `depth` and finds another */
   static Lane lane[32];
   for (int l = 0; l < 32; l++) lane[l].have = 0;
@@ -299,7 +301,7 @@ void wide8_warp_sim(const uint32_t* nodes, uint32_t n_nodes, const float* tris, 
     int idle = 0, busy = 0;
     for (int l = 0; l < 32; l++) { if (lane[l].have) busy++; else idle++; }
     if (next < n && (idle >= refill_min || busy == 0))
-      for (int l = 0; l < 32 && next < n; l++) if (!lane[l].have) lane_start(&lane[l], rays + 8 * (size_t)next++, n_nodes);
+      for (int l = 0; l < 32 && next < n; l++) if (!lane[l].have) { lane[l].idx = next; lane_start(&lane[l], rays + 8 * (size_t)next++, n_nodes); }
     busy = 0;
     for (int l = 0; l < 32; l++) busy += lane[l].have;
     if (!busy) break;
@@ -322,7 +324,7 @@ void wide8_warp_sim(const uint32_t* nodes, uint32_t n_nodes, const float* tris, 
         Lane* L = &lane[l];
         if (!L->have || !(L->T_mask | L->P_mask)) continue;
         out[3]++; out[5]++;
-        if (lane_tri(L, tris, tmin)) L->have = 0;
+        if (lane_tri(L, tris, tmin)) LANE_DONE(L);
       }
     }
     /* ---- node step */
@@ -338,10 +340,10 @@ void wide8_warp_sim(const uint32_t* nodes, uint32_t n_nodes, const float* tris, 
           else { L->Q_base[L->nq] = L->T_base; L->Q_mask[L->nq] = L->T_mask; L->nq++; }
           L->T_mask = 0;
         }
-        if (L->finished_nodes) { if (!L->P_mask) L->have = 0; continue; }
+        if (L->finished_nodes) { if (!L->P_mask) LANE_DONE(L); continue; }
       }
       if (lane_node(L, nodes, tmin)) { stepped++; out[4]++; }
-      else if (!(L->T_mask | L->P_mask)) L->have = 0;       /* no node left and no triangle pending: the ray is done */
+      else if (!(L->T_mask | L->P_mask)) LANE_DONE(L);      /* no node left and no triangle pending: the ray is done */
     }
     if (stepped) { out[0]++; out[1] += (uint64_t)stepped; }
   }
