@@ -10,12 +10,14 @@ the public API with the per-step host<->device copies inside the timed region.
 
 Workloads (BASELINE.json configs):
   mesh1m   config 3: Cornell walls + light and a 1,048,576-triangle displaced sphere, 1920x1080   (default)
+           (with --width 3840 --height 2160 --spp-per-step 1024: config 4)
   cornell  config 2: the reference's default scene at 1920x1080
   soup10m  config 5: 10,000,000 random triangles, max_depth 8
 
-N > 1: launched by torchrun, one rank per GPU.  Default sharding is split-spp (each rank renders
-`spp-per-step` of the N*spp-per-step frames of a step: fixed work per GPU, "weak"); `--shard tiles`
-splits the image instead ("strong").  The only collective is the accumulator reduce at the end.
+N > 1 (torchrun, one rank per GPU): STRONG scaling, as BASELINE.json states the configs -- the step's spp are split over
+the ranks (split-spp: rank r renders the frames with (sample-1) % N == r; `--shard tiles` splits the image instead), and
+every timed step ends with the collective: crt_combine (ncclReduce of the partial sums, or the gather of the owned tiles,
+inside libcrt) and rank 0's tone-map.  `--scaling weak` gives every rank the full spp per step (round-1 form).
 """
 from __future__ import annotations
 
@@ -39,10 +41,11 @@ TRI_BYTES = 48    # one triangle fetch (3 x float4)
 PIXEL_BYTES = 36  # accumulator read 16 + write 16 + framebuffer write 4, once per pixel per launch
 SHADE_PASS_BYTES = 232  # wf_logic per extension ray: S0..S5 + H written (112) and read back (112), live-list entry written + read (8)
 QUEUE_RAY_BYTES = 84  # wf_traverse per queued ray: queue entry 4 + origin 16 + direction 16 + exclude word 16 + hit read 16 + hit write 16
-
+FLOP_PER_RAY_LINEAR = 960.0   # ~0.96 kFLOP per intersect() on the reference's default scene, as written in the WGSL
 
 # frames per step = the samples per pixel BASELINE.json quotes for the config (configs[2], [1], [4])
 CONFIG_SPP = {"mesh1m": 256, "cornell": 64, "soup10m": 16}
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "r02_traffic.json")   # ncu dram__bytes per ray per kernel, rewritten by tools/gpu_round.sh
 
 
 def parse_args():
@@ -52,17 +55,22 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="mesh1m", choices=["mesh1m", "cornell", "soup10m"])
-    ap.add_argument("--spp-per-step", type=int, default=0, help="frames (samples per pixel) per step; 0 = the spp BASELINE.json quotes for the workload")
+    ap.add_argument("--spp-per-step", type=int, default=0, help="frames (samples per pixel) per step, all ranks together; 0 = the spp BASELINE.json quotes for the workload")
     ap.add_argument("--shard", default="spp", choices=["spp", "tiles"])
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N > 1: split the step's spp over the ranks (strong) or give every rank the full spp (weak)")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--frames-per-launch", type=int, default=0)
     ap.add_argument("--pool", type=int, default=0, help="wavefront path slots in flight (0 = library default)")
     ap.add_argument("--kernel", default="auto", choices=["auto", "mega", "wavefront"], help="force one form of the hot path (default: chosen from the scene)")
     ap.add_argument("--wf-split", action="store_true", help="wavefront: wf_shade + wf_regen kernels instead of the single wf_logic")
+    ap.add_argument("--bvh", default="auto", choices=["auto", "host", "device"], help="BVH builder: host binned SAH or device PLOC (auto: library default)")
+    ap.add_argument("--wf-tuning", type=lambda s: int(s, 0), default=0, help="crt_params.wf_tuning bits (include/crt.h)")
+    ap.add_argument("--bvh-tuning", type=lambda s: int(s, 0), default=0, help="crt_params.bvh_tuning bits: bins | 0x200 exact slots")
+    ap.add_argument("--bvh-prim-cost", type=float, default=0.0)
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-also", action="store_true", help="skip the secondary Cornell (config 2) measurement")
+    ap.add_argument("--no-also", action="store_true", help="skip the secondary measurements (Cornell config 2, single-frame dispatches, FP32 peak)")
     return ap.parse_args()
 
 
@@ -73,6 +81,14 @@ def workload_scene(name: str, width: int, height: int):
     if name == "cornell":
         return scenes.default_scene(width, height), 100, "config 2: reference default scene (16 patches, 2 spheres)"
     return scenes.soup_scene(width, height), 8, "config 5: 10,000,000-triangle random soup + Cornell walls/light, max_depth 8"
+
+
+def config_of(args, spp, max_depth, desc, world):
+    """The `config` object, the same in both arms (the reference arm states its bounded sample in `cpu_baseline.sample`)."""
+    return {"workload": f"{args.workload} ({desc})", "resolution": f"{args.width}x{args.height}", "spp_per_step": spp,
+            "max_depth": max_depth, "n_gpus": world,
+            "shard": "none" if world == 1 else f"{args.shard}, {args.scaling}",
+            "l2": "not flushed" if args.no_l2_flush else "flushed between steps (256 MiB write)"}
 
 
 def measured_peaks():
@@ -143,28 +159,25 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ CPU (oracle) legs
-def oracle_sample(ps_full, max_depth, width, height, frames, threads):
-    """Times the CPU oracle on a bounded sample: the same scene at a reduced resolution (same field of view)."""
+def oracle_scene(ps, max_depth):
+    """The CPU oracle on the SAME scene and resolution; the bounded sample is a number of whole frames."""
     from tests import orc   # bench.py's cpu_baseline / reference legs are allowed to use the oracle
-    import dataclasses
-    cam = ps_full.camera.copy()
-    cam[11], cam[12] = width, height
-    ps = dataclasses.replace(ps_full, camera=cam, width=width, height=height)
     n_tri = int((ps.primitives["category"] == 2).sum())
-    sc = orc.load().scene(ps, orc.default_params(max_depth=max_depth), use_bvh=n_tri > 0)
-    return sc, ps
+    return orc.load().scene(ps, orc.default_params(max_depth=max_depth), use_bvh=n_tri > 0)
 
 
 def run_reference(args):
     """--impl reference: the reference's own algorithm on the host cores (the CPU oracle port of its WGSL; the
-    WGSL itself cannot run here: no graphics stack, no node).  One step = one frame of a bounded sample."""
+    WGSL itself cannot run here: no graphics stack, no node).  Same scene, resolution and max_depth as the B200 arm; one
+    step = one frame (1 spp over the full image) -- a bounded sample of the step's spp, which a rate metric allows."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
     ps, max_depth, desc = workload_scene(args.workload, args.width, args.height)
+    spp = args.spp_per_step or CONFIG_SPP[args.workload]
     threads = os.cpu_count() or 1
-    sw, sh = args.width // 2, args.height // 2
-    sc, _ = oracle_sample(ps, max_depth, sw, sh, 1, threads)
+    sc = oracle_scene(ps, max_depth)
     sample = 0
     for _ in range(args.warmup):
         sc.render(1, sample_start=sample, threads=threads, want_fb=False)
@@ -178,13 +191,13 @@ def run_reference(args):
         rays += int(cnt[1]); shadow += int(cnt[2])
     dt = time.perf_counter() - t0
     value = rays / dt / 1e6
-    sample_desc = f"{sw}x{sh} x 1 frame per step of the same scene (1/4 of the pixels), {threads} threads"
+    sample_desc = f"1 frame (1 spp over the full {args.width}x{args.height} image) per step instead of {spp}, {threads} threads over image rows"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak" if world == 1 else args.scaling,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload} ({desc})", "resolution": f"{args.width}x{args.height}",
-                   "max_depth": max_depth, "sample": sample_desc},
+        "config": config_of(args, spp, max_depth, desc, max(world, args.gpus)),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample_desc},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "total_mrays_s": (rays + shadow) / dt / 1e6, "gpu_launches": 0,
@@ -194,99 +207,76 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
-def time_steps(r, stream, torch, steps, step_frames, flush_buf):
-    """K steps, each bracketed by its own CUDA events on the renderer's stream; L2 flushed between steps."""
+def time_steps(r, stream, torch, steps, frames, flush_buf, combine):
+    """K steps, each bracketed by its own CUDA events on the renderer's stream; L2 flushed between steps.  A step is the
+    frames plus -- on more than one GPU -- the combine (collective + rank 0's tone-map), all enqueued asynchronously."""
     evs = []
+    comb = []
     for _ in range(steps):
         if flush_buf is not None:
             with torch.cuda.stream(stream):
                 flush_buf.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        r.frame(step_frames)
+        r.frame(frames)
+        if combine:
+            r.combine(0)
         e1.record(stream)
         evs.append((e0, e1))
+        if combine:
+            stream.synchronize()                  # crt_last_combine reads the most recent combine's events
+            comb.append(r.last_combine())
     stream.synchronize()
-    return [a.elapsed_time(b) for a, b in evs]
-
-
-def measure(r, stream, torch, dist, args, world, step_frames, flush_buf, device, combine_fn):
-    r.reset(); r.reset_counters()
-    time_steps(r, stream, torch, args.warmup, step_frames, flush_buf)
-    c0 = r.counters()
-    k0 = r.kernel_times()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize(device)
-    with ClockSampler(device) as clk:
-        ms = time_steps(r, stream, torch, args.steps, step_frames, flush_buf)
-        comb_ms = 0.0
-        if world > 1:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
-            combine_fn()
-            e1.record(stream)
-            stream.synchronize()
-            comb_ms = e0.elapsed_time(e1)
-        torch.cuda.synchronize(device)
-        if world > 1:
-            dist.barrier()
-    c1 = r.counters()
-    k1 = r.kernel_times()
-    d = {k: c1[k] - c0[k] for k in c1}
-    kt = {k: (k1[k][0] - k0[k][0], k1[k][1] - k0[k][1]) for k in k1}
-    return ms, comb_ms, d, clk.summary(), kt
+    return [a.elapsed_time(b) for a, b in evs], comb
 
 
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from computeraytracer_b200 import multi
-    from computeraytracer_b200.renderer import SHARD_SPLIT_SPP, SHARD_TILES, Renderer
+    from computeraytracer_b200.renderer import (BVH_BUILDER_DEVICE, BVH_BUILDER_HOST_SAH, SHARD_SPLIT_SPP, SHARD_TILES, Renderer)
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: libcrt has no CPU fallback")
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a B200: libcrt has no CPU fallback")
     device = local
     torch.cuda.set_device(device)
     stream = torch.cuda.Stream(device)
+    dev = f"cuda:{device}"
 
     ps, max_depth, desc = workload_scene(args.workload, args.width, args.height)
     r = Renderer(device)
     r.set_stream(stream.cuda_stream)
+    bvh_bits = args.bvh_tuning | {"auto": 0, "host": BVH_BUILDER_HOST_SAH, "device": BVH_BUILDER_DEVICE}[args.bvh]
+    base = dict(max_depth=max_depth, frames_per_launch=args.frames_per_launch, wf_slots=args.pool,
+                kernel={"auto": 0, "mega": 1, "wavefront": 2}[args.kernel], wf_tuning=args.wf_tuning, bvh_tuning=bvh_bits,
+                bvh_prim_cost=args.bvh_prim_cost, flags=4 if args.wf_split else 0)
+    r.set_params(**base)
     t0 = time.perf_counter()
     r.set_scene(ps)
-    p = r.set_params(max_depth=max_depth, frames_per_launch=args.frames_per_launch)
-    if args.pool or args.wf_split or args.kernel != "auto":
-        p.wf_slots = args.pool
-        p.kernel = {"auto": 0, "mega": 1, "wavefront": 2}[args.kernel]
-        if args.wf_split:
-            p.flags |= 4   # CRT_FLAG_WF_SPLIT
-        r.set_params(p)
     st = r.scene_stats()   # forces the scene-upload module to run (SoA repack + BVH build)
     r.synchronize()
     setup_s = time.perf_counter() - t0
 
     spp = args.spp_per_step or CONFIG_SPP[args.workload]
-    if world > 1 and args.shard == "spp":
-        r.set_shard(rank, world, SHARD_SPLIT_SPP)
-        step_frames, scaling = spp * world, "weak"
-    elif world > 1:
-        r.set_shard(rank, world, SHARD_TILES)
-        step_frames, scaling = spp, "strong"
+    combine = world > 1
+    if world > 1:
+        mode = SHARD_SPLIT_SPP if args.shard == "spp" else SHARD_TILES
+        multi.init(r, mode)            # NCCL communicator inside libcrt; torch.distributed only carried the 128-byte id
+        frames = spp * world if (args.scaling == "weak" and args.shard == "spp") else spp
+        scaling = args.scaling if args.shard == "spp" else "strong"
     else:
-        step_frames, scaling = spp, "weak"
-    flush_buf = None if args.no_l2_flush else torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{device}")
-    combine_fn = (lambda: multi.combine(r, stream)) if world > 1 else (lambda: None)
+        frames, scaling = spp, "weak"
+    flush_buf = None if args.no_l2_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     # ---- calibration pass with the detailed counters (separate, slower kernel variant; not timed)
     r.reset(); r.reset_counters(); r.enable_stats(True)
-    r.frame(step_frames); r.synchronize()
+    r.frame(frames); r.synchronize()
     cal = r.counters()
     r.enable_stats(False)
     cal_rays = cal["rays_ext"] + cal["rays_shadow"]
@@ -295,75 +285,122 @@ def run_b200(args):
     # consumed); every path stages 16 B of XYZ.  Per (extension + shadow) ray, like bytes_per_ray.
     logic_bytes_per_ray = (SHADE_PASS_BYTES * cal["rays_ext"] + 16 * cal["paths"]) / max(cal_rays, 1)
 
-    # ---- device-timed region (events between the hot-path launches give the per-kernel-class times)
+    # ---- instrumented pass: CUDA events between the hot-path launches (host-driven loop) give the per-kernel-class times the
+    # roofline is computed from.  The headline below runs the default path (the loop on the device) and is timed as a whole.
+    r.reset(); r.reset_counters()
     r.enable_kernel_times(True)
-    ms, comb_ms, d, clocks, kt = measure(r, stream, torch, dist, args, world, step_frames, flush_buf, device, combine_fn)
-    total_ms = torch.tensor([sum(ms) + comb_ms], dtype=torch.float64, device=f"cuda:{device}")
-    tot = torch.tensor([d["rays_ext"], d["rays_shadow"], d["paths"], d["launches"]], dtype=torch.float64, device=f"cuda:{device}")
+    time_steps(r, stream, torch, 1, frames, flush_buf, combine)
+    r.reset_counters()
+    n_inst = max(1, min(3, args.steps))
+    ms_inst, _ = time_steps(r, stream, torch, n_inst, frames, flush_buf, combine)
+    kt = r.kernel_times()
+    d_inst = r.counters()
+    r.enable_kernel_times(False)
+
+    # ---- device-timed region, default path
+    r.reset(); r.reset_counters()
+    time_steps(r, stream, torch, args.warmup, frames, flush_buf, combine)    # includes the warm-up combines (NCCL channels set up)
+    c0 = r.counters()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    with ClockSampler(device) as clk:
+        ms, comb = time_steps(r, stream, torch, args.steps, frames, flush_buf, combine)
+        torch.cuda.synchronize(device)
+        if world > 1:
+            dist.barrier()
+    clocks = clk.summary()
+    c1 = r.counters()
+    d = {k: c1[k] - c0[k] for k in c1}
+    total_ms = torch.tensor([sum(ms)], dtype=torch.float64, device=dev)
+    tot = torch.tensor([d["rays_ext"], d["rays_shadow"], d["paths"], d["launches"]], dtype=torch.float64, device=dev)
+    comb_t = torch.tensor([sum(c[0] for c in comb) / max(len(comb), 1), float(sum(c[1] for c in comb)) / max(len(comb), 1)],
+                          dtype=torch.float64, device=dev)
+    comb_max = comb_t.clone()
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(comb_max, op=dist.ReduceOp.MAX)
+        dist.all_reduce(comb_t, op=dist.ReduceOp.SUM)
     job_ms = float(total_ms.item())
     rays_ext, rays_shadow, paths, launches = [float(x) for x in tot.tolist()]
     value = rays_ext / (job_ms * 1e-3) / 1e6
 
-    r.enable_kernel_times(False)
-
-    # ---- roofline of the dominant kernel class, this rank's launches, from the events of the timed region
+    # ---- roofline of the dominant kernel class, this rank's launches, from the events of the instrumented pass
     peak, peak_src = measured_peaks()
     kt = {k: v for k, v in kt.items() if v[1] > 0}
     kernel = max(kt, key=lambda k: kt[k][0]) if kt else "pt_megakernel"
-    k_ms, k_n = kt.get(kernel, (sum(ms), max(d["launches"], 1)))
+    k_ms, k_n = kt.get(kernel, (sum(ms_inst), max(d_inst["launches"], 1)))
     launch_ms = k_ms / max(k_n, 1)
-    my_rays = d["rays_ext"] + d["rays_shadow"]
+    inst_rays = d_inst["rays_ext"] + d_inst["rays_shadow"]
     pixels_per_step = args.width * args.height / (world if (world > 1 and args.shard == "tiles") else 1)
+    l2_resident = (st["bvh_bytes"] + st["tri_bytes"]) < 100e6
     if kernel == "pt_megakernel":
-        total_bytes = bytes_per_ray * my_rays + PIXEL_BYTES * pixels_per_step * k_n
+        total_bytes = bytes_per_ray * inst_rays + PIXEL_BYTES * pixels_per_step * k_n
         what = "80 B x BVH nodes visited + 48 B x triangles tested (device counters) + 36 B x pixels per launch"
     elif kernel in ("wf_shade", "wf_logic"):   # path-state traffic: S0..S5 + H read and written once per bounce, queue entries
-        total_bytes = logic_bytes_per_ray * my_rays
+        total_bytes = logic_bytes_per_ray * inst_rays
         what = "232 B of path state (S0..S5, H read + written, live-list entry) x extension rays + 16 B of staged XYZ x paths (device counters)"
     else:   # wf_traverse (a BVH scene): the traversal kernel's own fetches
-        total_bytes = bytes_per_ray * my_rays
+        total_bytes = bytes_per_ray * inst_rays
         what = "80 B x BVH nodes visited + 48 B x triangles tested + 84 B x rays queued (device counters of a calibration step)"
     algo_bytes = total_bytes / max(k_n, 1)
     achieved = algo_bytes / (launch_ms * 1e-3) / 1e9
+    if st["n_triangles"] == 0:
+        regime = "linear list: FP32 pipe / instruction issue (HBM sees 36 B per pixel and launch + the wavefront's path state)"
+    elif l2_resident:
+        regime = "L2-resident scene: fetch bandwidth out of L2/L1 and load latency x lane occupancy; `frac` is a fraction of the HBM copy peak used as a yardstick, `dram_frac` is the real DRAM utilisation"
+    else:
+        regime = "scene larger than L2: HBM bandwidth"
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": kernel, "launch_ms": launch_ms, "launches": k_n, "share_of_step": k_ms / max(sum(ms), 1e-9),
+                "dram_frac": None, "regime": regime,
+                "kernel": kernel, "launch_ms": launch_ms, "launches": k_n, "share_of_step": k_ms / max(sum(ms_inst), 1e-9),
                 "algorithmic_bytes_per_launch": algo_bytes,
                 "bytes_per_ray": bytes_per_ray, "nodes_per_ray": cal["node_visits"] / max(cal_rays, 1),
                 "tris_per_ray": cal["tri_tests"] / max(cal_rays, 1), "bvh_rays_per_ray": cal["bvh_rays"] / max(cal_rays, 1),
                 "peak_source": peak_src,
-                "kernels_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
+                "kernels_ms_per_step": {k: v[0] / n_inst for k, v in kt.items()},
+                "instrumented_ms_per_step": sum(ms_inst) / n_inst,
                 "note": "algorithmic bytes = " + what + "; fetches served by L1/L2 count, so they exceed DRAM traffic "
-                        "when the scene is L2-resident (see DESIGN.md section 6)"}
+                        "when the scene is L2-resident (see DESIGN.md section 6).  Per-kernel times: CUDA events between the launches of "
+                        "an instrumented pass (host-driven loop); the headline runs the device-side loop and is timed as a whole"}
     # both wavefront kernels side by side (they take about half of a step each, so which one is "dominant" can flip
     # from run to run): wf_traverse against its fetch bytes, wf_logic against its path-state bytes
+    traffic = {}
+    if os.path.exists(TRAFFIC_FILE):   # ncu-measured DRAM bytes per ray per kernel at this HEAD (tools/gpu_round.sh rewrites the file)
+        try:
+            with open(TRAFFIC_FILE) as f:
+                traffic = json.load(f).get(args.workload, {})
+        except Exception:
+            traffic = {}
     if "wf_traverse" in kt and "wf_logic" in kt:
         both = {}
-        for name, tb in (("wf_traverse", bytes_per_ray * my_rays),
-                         ("wf_logic", logic_bytes_per_ray * my_rays)):
+        for name, tb in (("wf_traverse", bytes_per_ray * inst_rays), ("wf_logic", logic_bytes_per_ray * inst_rays)):
             ms_k, n_k = kt[name]
             gbs = tb / max(ms_k * 1e-3, 1e-12) / 1e9
             both[name] = {"achieved": gbs, "frac": gbs / peak, "launch_ms": ms_k / max(n_k, 1), "launches": n_k,
-                          "share_of_step": ms_k / max(sum(ms), 1e-9)}
-        roofline["per_kernel"] = both
-    prof = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(prof):   # ncu-measured DRAM bytes per ray of this kernel (see the file), scaled to this run's launches
-        try:
-            with open(prof) as f:
-                per_ray = json.load(f).get(args.workload, {}).get(kernel, {}).get("dram_bytes_per_ray")
+                          "share_of_step": ms_k / max(sum(ms_inst), 1e-9)}
+            per_ray = traffic.get(name, {}).get("dram_bytes_per_ray")
             if per_ray is not None and args.width == 1920 and args.height == 1080:
-                roofline["traffic"] = per_ray * my_rays / max(k_n, 1)
-                roofline["traffic_source"] = "profiles/r01_traffic.json (ncu launch list, cold L2 per launch)"
-        except Exception:
-            pass
+                dram = per_ray * inst_rays
+                both[name]["dram_gbs"] = dram / max(ms_k * 1e-3, 1e-12) / 1e9
+                both[name]["dram_frac"] = both[name]["dram_gbs"] / peak
+                both[name]["traffic_over_algorithmic"] = dram / max(tb, 1)
+        roofline["per_kernel"] = both
+    per_ray = traffic.get(kernel, {}).get("dram_bytes_per_ray")
+    if per_ray is not None and args.width == 1920 and args.height == 1080:
+        roofline["traffic"] = per_ray * inst_rays / max(k_n, 1)
+        roofline["dram_frac"] = roofline["traffic"] / (launch_ms * 1e-3) / 1e9 / peak
+        roofline["traffic_source"] = os.path.relpath(TRAFFIC_FILE, ROOT) + " (ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, cold L2 per launch under ncu)"
 
     # ---- end to end through the public API with host buffers
     fb_host = torch.empty((args.height, args.width, 4), dtype=torch.uint8).pin_memory().numpy()
     cam_host = ps.camera.copy()
     r.reset(); r.reset_counters()
-    r.frame(step_frames); r.framebuffer(fb_host)   # warm-up
+    r.frame(frames)
+    if combine:
+        r.combine(0)
+    r.framebuffer(fb_host)   # warm-up
     e0 = r.counters()
     if world > 1:
         dist.barrier()
@@ -371,25 +408,29 @@ def run_b200(args):
     t0 = time.perf_counter()
     for _ in range(args.steps):
         r.set_camera(cam_host)          # H2D: the step's input (64 B camera; the scene stays resident)
-        r.frame(step_frames)
-        r.framebuffer(fb_host)          # D2H: the step's result (RGBA8 frame), synchronises
-    if world > 1:
-        combine_fn()
+        r.frame(frames)
+        if combine:
+            r.combine(0)                # the collective, then the image is rank 0's
         if rank == 0:
-            r.framebuffer(fb_host)
+            r.framebuffer(fb_host)      # D2H: the step's result (RGBA8 frame, combined), synchronises
+        else:
+            r.synchronize()
     r.synchronize()
     e2e_s = time.perf_counter() - t0
     e1 = r.counters()
-    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=f"cuda:{device}")
-    e2e_r = torch.tensor([e1["rays_ext"] - e0["rays_ext"]], dtype=torch.float64, device=f"cuda:{device}")
+    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    e2e_r = torch.tensor([e1["rays_ext"] - e0["rays_ext"]], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
         dist.all_reduce(e2e_r, op=dist.ReduceOp.SUM)
-    e2e = {"value": float(e2e_r.item()) / float(e2e_t.item()) / 1e6, "unit": UNIT, "h2d_bytes_per_step": 64,
+    e2e_val = float(e2e_r.item()) / float(e2e_t.item()) / 1e6
+    e2e = {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": 64,
            "d2h_bytes_per_step": int(fb_host.nbytes), "wall_s": float(e2e_t.item()),
            "setup_s_not_included": setup_s,
-           "note": "per step: camera upload, frames, RGBA8 framebuffer readback to pinned host memory; "
-                   "scene upload + BVH build is one-off setup, reported separately"}
+           "with_setup": {"value": float(e2e_r.item()) / (float(e2e_t.item()) + setup_s) / 1e6, "unit": UNIT,
+                          "note": f"the same {args.steps} steps plus the one-off scene upload (SoA repack + BVH build, {setup_s:.2f} s)"},
+           "note": "per step: camera upload, frames, (N > 1: crt_combine), RGBA8 framebuffer readback to pinned host memory on rank 0; "
+                   "scene upload + BVH build is one-off setup, reported separately and in with_setup"}
 
     line = None
     if rank == 0:
@@ -397,50 +438,90 @@ def run_b200(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": job_ms / args.steps, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload} ({desc})", "resolution": f"{args.width}x{args.height}",
-                       "spp_per_step": spp, "frames_per_step_all_ranks": step_frames, "total_spp": step_frames * args.steps,
-                       "max_depth": max_depth, "shard": ("none" if world == 1 else args.shard),
-                       "l2": "not flushed" if args.no_l2_flush else "flushed between steps (256 MiB write)",
-                       "primitives": st["n_prims"], "triangles": st["n_triangles"], "bvh_nodes": st["bvh_nodes"],
-                       "bvh_depth": st["bvh_depth"], "scene_bytes": st["bvh_bytes"] + st["tri_bytes"]},
-            "ms_per_frame": job_ms / (args.steps * spp),
+            "config": config_of(args, spp, max_depth, desc, world),
+            "scene": {"primitives": st["n_prims"], "triangles": st["n_triangles"], "bvh_nodes": st["bvh_nodes"],
+                      "bvh_depth": st["bvh_depth"], "scene_bytes": st["bvh_bytes"] + st["tri_bytes"], "bvh_builder": st["builder"]},
+            "frames_per_step_all_ranks": frames, "total_spp": frames * args.steps,
+            "ms_per_frame": job_ms / (args.steps * frames),
             "total_mrays_s": (rays_ext + rays_shadow) / (job_ms * 1e-3) / 1e6,
             "rays": {"ext": rays_ext, "shadow": rays_shadow, "paths": paths},
-            "combine_ms": comb_ms, "setup_s": setup_s, "bvh_build_ms": st["build_us"] / 1e3,
+            "setup_s": setup_s, "scene_upload_ms": st["build_us"] / 1e3, "bvh_build_ms": st["tree_us"] / 1e3,
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "e2e": e2e,
         }
+        if combine:
+            line["combine"] = {"ms_per_step_max_over_ranks": float(comb_max[0].item()), "ms_per_step_mean_over_ranks": float(comb_t[0].item()) / world,
+                               "bytes_sent_per_step_all_ranks": float(comb_t[1].item()),
+                               "what": ("ncclReduce(SUM) of the W*H*4 f32 partial sums into rank 0's combined buffer" if args.shard == "spp"
+                                        else "grouped ncclSend/ncclRecv of the owned tiles only") + " + rank 0's tone-map, inside every timed step (libcrt crt_combine)",
+                               "note": "device time between the events around crt_combine on each rank's stream; it includes waiting for the slowest rank's frames"}
+            line["combine_ms"] = float(comb_max[0].item())
 
-    # ---- rank 0, N = 1 only: CPU baseline and the secondary Cornell figure
+    # ---- rank 0, N = 1 only: CPU baseline, single-frame dispatches, FP32 peak and the secondary Cornell figure
     if rank == 0 and world == 1:
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            sw, sh = args.width // 2, args.height // 2
-            sc, _ = oracle_sample(ps, max_depth, sw, sh, 1, threads)
-            budget_s, frames, ext, shadow, sample = 12.0, 0, 0, 0, 0
+            sc = oracle_scene(ps, max_depth)
+            budget_s, nf, ext, shadow, sample = 12.0, 0, 0, 0, 0
             t0 = time.perf_counter()
-            while time.perf_counter() - t0 < budget_s:   # whole frames of the same scene until ~12 s of CPU work
+            while time.perf_counter() - t0 < budget_s:   # whole frames of the same scene at the same resolution until ~12 s of CPU work
                 _, _, cnt = sc.render(1, sample_start=sample, threads=threads, want_fb=False)
-                sample += 1; frames += 1
+                sample += 1; nf += 1
                 ext += int(cnt[1]); shadow += int(cnt[2])
             dt = time.perf_counter() - t0
             line["cpu_baseline"] = {"value": ext / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": f"{sw}x{sh} x {frames} frames of the same scene, same max_depth ({dt:.1f} s of CPU work, "
-                                              f"{threads} threads over image rows)",
+                                    "sample": f"{nf} frames (1 spp each over the full {args.width}x{args.height} image) of the same scene, same max_depth "
+                                              f"({dt:.1f} s of CPU work, {threads} threads over image rows)",
                                     "total_mrays_s": (ext + shadow) / dt / 1e6}
-        if not args.no_also and args.workload != "cornell":
-            from computeraytracer_b200 import scenes
-            r.set_scene(scenes.default_scene(args.width, args.height))
-            r.set_params(max_depth=100)
-            r.reset(); r.reset_counters()
-            spp2 = CONFIG_SPP["cornell"]
-            ms2 = time_steps(r, stream, torch, 2, spp2, flush_buf)
-            c0 = r.counters()
-            ms2 = time_steps(r, stream, torch, 8, spp2, flush_buf)
-            c1 = r.counters()
-            line["also"] = {"workload": "cornell (config 2: reference default scene, 1920x1080, max_depth 100)",
-                            "value": (c1["rays_ext"] - c0["rays_ext"]) / (sum(ms2) * 1e-3) / 1e6, "unit": UNIT,
-                            "total_mrays_s": (c1["rays_ext"] + c1["rays_shadow"] - c0["rays_ext"] - c0["rays_shadow"]) / (sum(ms2) * 1e-3) / 1e6,
-                            "ms_per_frame": sum(ms2) / (8 * spp2), "steps": 8, "spp_per_step": spp2}
+        if not args.no_also:
+            # the reference's own usage: frame() = one dispatch of one frame per refresh (src/main.js:584-621)
+            def single_frames(n=64):
+                r.reset(); r.reset_counters()
+                for _ in range(8):
+                    r.frame(1)
+                r.synchronize()
+                c_a = r.counters()
+                ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t_a = time.perf_counter()
+                ea.record(stream)
+                for _ in range(n):
+                    r.frame(1)
+                eb.record(stream)
+                t_enq = time.perf_counter() - t_a
+                stream.synchronize()
+                c_b = r.counters()
+                msd = ea.elapsed_time(eb)
+                return {"dispatches": n, "ms_per_dispatch": msd / n, "host_ms_per_call": t_enq / n * 1e3,
+                        "value": (c_b["rays_ext"] - c_a["rays_ext"]) / (msd * 1e-3) / 1e6, "unit": UNIT,
+                        "note": "crt_dispatch_frames(1) x n back to back (the reference's frame loop), device-timed as a whole; "
+                                "host_ms_per_call is how long a call keeps the host"}
+            line["single_frame"] = {args.workload: single_frames()}
+            try:
+                fp32 = r.measure_fp32_tflops()
+            except Exception:
+                fp32 = None
+            line["fp32_peak_tflops_measured"] = fp32
+            if args.workload != "cornell":
+                from computeraytracer_b200 import scenes
+                r.set_scene(scenes.default_scene(args.width, args.height))
+                r.set_params(max_depth=100)
+                r.reset(); r.reset_counters()
+                spp2 = CONFIG_SPP["cornell"]
+                time_steps(r, stream, torch, 2, spp2, flush_buf, False)
+                c0 = r.counters()
+                ms2, _ = time_steps(r, stream, torch, 8, spp2, flush_buf, False)
+                c1 = r.counters()
+                tot2 = (c1["rays_ext"] + c1["rays_shadow"] - c0["rays_ext"] - c0["rays_shadow"])
+                also = {"workload": "cornell (config 2: reference default scene, 1920x1080, max_depth 100)",
+                        "value": (c1["rays_ext"] - c0["rays_ext"]) / (sum(ms2) * 1e-3) / 1e6, "unit": UNIT,
+                        "total_mrays_s": tot2 / (sum(ms2) * 1e-3) / 1e6,
+                        "ms_per_frame": sum(ms2) / (8 * spp2), "steps": 8, "spp_per_step": spp2}
+                if fp32:
+                    tf = tot2 * FLOP_PER_RAY_LINEAR / (sum(ms2) * 1e-3) / 1e12
+                    also["roofline"] = {"bound": "fp32", "achieved": tf, "peak": fp32, "unit": "TFLOP/s", "frac": tf / fp32,
+                                        "note": "0.96 kFLOP per intersect() as written in the WGSL (SURVEY 8d) x all rays, against the FP32 FMA rate "
+                                                "measured in this run; the kernels hoist ray invariants, so the executed count is about half"}
+                line["also"] = also
+                line["single_frame"]["cornell"] = single_frames()
     r.close()
     if world > 1:
         dist.barrier()

@@ -12,8 +12,8 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcrt.so")
-SOURCES = ["crt_api.cu", "crt_kernels.cu", "crt_wavefront.cu", "crt_bvh.cpp"]
-HEADERS = ["crt_device.cuh", "crt_path.cuh", "crt_kernels.h", "crt_wavefront.h", "crt_bvh.h", "../../include/crt.h", "../../include/crt_detmath.h"]
+SOURCES = ["crt_api.cu", "crt_kernels.cu", "crt_wavefront.cu", "crt_bvh_device.cu", "crt_bvh.cpp"]
+HEADERS = ["crt_device.cuh", "crt_path.cuh", "crt_kernels.h", "crt_wavefront.h", "crt_bvh.h", "crt_bvh_ploc.h", "crt_bvh_device.h", "../../include/crt.h", "../../include/crt_detmath.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -6,6 +6,7 @@
 // boxes are padded so that culling is conservative with respect to the f32 rounding of those tests
 // (DESIGN.md "Conservative culling").  Tree shape therefore affects speed, never results.
 #include "crt_bvh.h"
+#include "crt_bvh_ploc.h"
 
 #include <algorithm>
 #include <atomic>
@@ -14,15 +15,16 @@
 #include <cstring>
 #include <future>
 #include <limits>
+#include <numeric>
 
 namespace crt {
 namespace {
 
-constexpr int kBinsDefault = 32, kBinsMax = 256;   // SAH bins per axis; tuning override CRT_BVH_BINS (tools/bvh_eval.py)
+constexpr int kBinsDefault = 32, kBinsMax = 256;   // SAH bins per axis (BvhOptions::bins; 128 bins + exact slots: wf_traverse -1.7 %, profiles/r02a_traverse_schedule_ab.txt)
 constexpr uint32_t kLeafMax = 3;         // a wide node's meta byte holds the leaf's triangle count in 3 unary bits
 constexpr uint32_t kBvh2LeafMax = 1;     // the binary tree is split down to single triangles; the collapse decides the leaves
 constexpr float kNodeCost = 1.0f;        // SAH weights of the collapse (Ylitie et al. 2017, section 4.1); the triangle weight
-constexpr float kPrimCostDefault = 0.75f; // (measured 0.3 .. 1.5 on mesh1m and soup10m: flat above 0.75; 0.3 is 1 % / 5 % slower); tuning override: CRT_BVH_PRIM_COST
+// (BvhOptions::prim_cost, default 0.75; measured 0.3 .. 1.5 on mesh1m and soup10m: flat above 0.75; 0.3 is 1 % / 5 % slower)
 constexpr uint32_t kForceMedianDepth = 36;
 constexpr float kTraversalCost = 1.0f;   // relative to one triangle test
 
@@ -165,7 +167,16 @@ inline int scale_exp(float ext) {
 
 }  // namespace
 
-void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n_threads, BvhResult& out) {
+BvhOptions bvh_options(uint32_t bvh_tuning, float prim_cost) {
+  BvhOptions o;
+  const int bins = (int)(bvh_tuning & 0x1FFu);
+  if (bins >= 4 && bins <= kBinsMax) o.bins = bins;
+  o.optimal_slots = (bvh_tuning & 0x200u) != 0u;
+  if (prim_cost > 0.0f) o.prim_cost = prim_cost;
+  return o;
+}
+
+void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n_threads, const BvhOptions& opt, BvhResult& out) {
   out.nodes.clear(); out.tri_src.clear(); out.n_nodes = 0; out.max_depth = 0; out.pad = 0.0f;
   const size_t n = tri_pos.size();
   if (!n) return;
@@ -185,23 +196,26 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
     scene.grow(it.lo, it.hi);
   }
   const float ext = std::max(scene.hi[0] - scene.lo[0], std::max(scene.hi[1] - scene.lo[1], scene.hi[2] - scene.lo[2]));
-  const float pad = std::max(ext, 1.0f) * (1.0f / 32768.0f);
+  // The padding has to cover what f32 does to the triangles themselves, not only the extent of the mesh: a vertex v0 + e1 and
+  // the difference o - v0 are rounded to an ulp of the COORDINATE, so a mesh of extent 2 around x = 2000 needs a pad that
+  // scales with 2000 (ext / 32768 would be below one ulp there and vanish in lo - pad).
+  float maxabs = 0.0f;
+  for (int a = 0; a < 3; a++) maxabs = std::max(maxabs, std::max(std::fabs(scene.lo[a]), std::fabs(scene.hi[a])));
+  const float pad = std::max(std::max(ext, maxabs), 1.0f) * (1.0f / 32768.0f);
   out.pad = pad;
   for (int a = 0; a < 3; a++) { out.lo[a] = scene.lo[a] - pad; out.hi[a] = scene.hi[a] + pad; }
 
   Builder b(items, n_threads < 1 ? 1 : n_threads);
-  if (const char* e = std::getenv("CRT_BVH_BINS")) { const int v = std::atoi(e); if (v >= 4 && v <= kBinsMax) b.kBins = v; }
+  b.kBins = opt.bins;
   b.build(0, 0, (uint32_t)n, 0);
   const std::vector<BNode>& pool = b.pool;
 
-  bool optimal_slots = false;
-  if (const char* e = std::getenv("CRT_BVH_SLOTS")) optimal_slots = std::atoi(e) == 1;
+  const bool optimal_slots = opt.optimal_slots;
   // ---- which BVH2 subtrees become wide nodes, which become leaves: the SAH-optimal collapse of Ylitie et al. (2017,
   // section 4.1) by dynamic programming.  cost[n][i-1] = cheapest way to represent the subtree of n as at most i
   // children of a wide node (i = 1: one child, either a leaf of <= 3 triangles or a wide node of its own).
   const uint32_t n_bvh2 = b.next.load();
-  float kPrimCost = kPrimCostDefault;
-  if (const char* e = std::getenv("CRT_BVH_PRIM_COST")) { const float v = std::strtof(e, nullptr); if (v > 0.0f) kPrimCost = v; }
+  const float kPrimCost = opt.prim_cost;
   std::vector<float> cost((size_t)n_bvh2 * 7);
   std::vector<uint8_t> dec((size_t)n_bvh2 * 8);   // [0..6]: split for i = 1..7 (0 = "same as i-1"; for i = 1: 0 = leaf, else split of the wide node); 
   const float inf = std::numeric_limits<float>::infinity();
@@ -283,7 +297,7 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
       slot_of[bi] = bs; slot_used[bs] = true; child_done[bi] = true;
     }
     if (optimal_slots) {
-      // tuning (CRT_BVH_SLOTS=1): the assignment that maximises the summed score exactly, by dynamic programming over the
+      // tuning (BvhOptions::optimal_slots): the assignment that maximises the summed score exactly, by dynamic programming over the
       // sets of used slots (child k takes a free slot of a set with k slots used)
       float score[8][8];
       for (int i = 0; i < nc; i++) {
@@ -349,6 +363,77 @@ void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n
     out.max_depth = std::max(out.max_depth, wide_depth[k]);
   }
   out.n_nodes = (uint32_t)wide_src.size();
+}
+
+// The device build's algorithm (crt_bvh_ploc.h: Morton sort, PLOC with the collapse's dynamic programme, level-by-level
+// emission) driven by plain loops on the host.  The CUDA kernels of crt_bvh_device.cu run the same per-element functions
+// with one thread per index; this driver exists so that the CPU test-suite can check that logic against the builder
+// invariants without a GPU (crt_host_build_bvh with CRT_BVH_BUILDER_DEVICE).  Single-threaded, not a product path.
+void build_bvh_ploc_host(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, const BvhOptions& opt, BvhResult& out) {
+  using namespace ploc;
+  out.nodes.clear(); out.tri_src.clear(); out.n_nodes = 0; out.max_depth = 0; out.pad = 0.0f;
+  const uint32_t n = (uint32_t)tri_pos.size();
+  if (!n) return;
+  std::vector<Box3> boxes_in(n);
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (uint32_t i = 0; i < n; i++) {
+    boxes_in[i] = tri_box(prims, tri_pos[i]);
+    for (int a = 0; a < 3; a++) {
+      lo[a] = std::min(lo[a], boxes_in[i].lo[a]); hi[a] = std::max(hi[a], boxes_in[i].hi[a]);
+      const float c = 0.5f * (boxes_in[i].lo[a] + boxes_in[i].hi[a]);
+      clo[a] = std::min(clo[a], c); chi[a] = std::max(chi[a], c);
+    }
+  }
+  float ext = 0.0f, maxabs = 0.0f;
+  for (int a = 0; a < 3; a++) { ext = std::max(ext, hi[a] - lo[a]); maxabs = std::max(maxabs, std::max(std::fabs(lo[a]), std::fabs(hi[a]))); }
+  const float pad = std::max(std::max(ext, maxabs), 1.0f) * (1.0f / 32768.0f);
+  out.pad = pad;
+  for (int a = 0; a < 3; a++) { out.lo[a] = lo[a] - pad; out.hi[a] = hi[a] + pad; }
+  std::vector<uint64_t> keys(n);
+  std::vector<uint32_t> sorted(n);
+  for (uint32_t i = 0; i < n; i++) keys[i] = morton63(boxes_in[i], clo, chi);
+  std::iota(sorted.begin(), sorted.end(), 0u);
+  std::stable_sort(sorted.begin(), sorted.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });   // the radix sort is stable too
+
+  const size_t n2 = 2 * (size_t)n;
+  std::vector<Box3> box(n2); std::vector<uint32_t> left(n2), right(n2), total(n2); std::vector<float> cost(n2 * 7); std::vector<uint8_t> dec(n2 * 8);
+  Tree t; t.n_leaves = n; t.box = box.data(); t.left = left.data(); t.right = right.data(); t.total = total.data(); t.cost = cost.data(); t.dec = dec.data();
+  std::vector<uint32_t> leaf_tri(n), cl_a(n), cl_b(n), nn(n);
+  std::vector<uint64_t> word(std::max<size_t>(n, 1)), scan(std::max<size_t>(n, 1));
+  for (uint32_t k = 0; k < n; k++) { box[k] = boxes_in[sorted[k]]; total[k] = 1; dp_node(t, k, opt.prim_cost); leaf_tri[k] = tri_pos[sorted[k]]; cl_a[k] = k; }
+  uint32_t n_cl = n, n_nodes2 = n;
+  while (n_cl > 1) {
+    for (uint32_t i = 0; i < n_cl; i++) nn[i] = find_nn(t, cl_a.data(), n_cl, i);
+    uint64_t acc = 0;
+    for (uint32_t i = 0; i < n_cl; i++) { word[i] = merge_word(nn.data(), i); scan[i] = acc; acc += word[i]; }
+    for (uint32_t i = 0; i < n_cl; i++) apply_merge(t, cl_a.data(), nn.data(), word.data(), scan.data(), i, n_nodes2, opt.prim_cost, cl_b.data());
+    n_cl = (uint32_t)(acc & 0xFFFFFFFFull); n_nodes2 += (uint32_t)(acc >> 32);
+    cl_a.swap(cl_b);
+  }
+  const uint32_t root = n_nodes2 - 1u;
+  std::vector<uint32_t> frontier_a{root}, frontier_b;
+  EmitParams ep; ep.pad = pad; ep.exact_slots = opt.optimal_slots ? 1u : 0u;
+  out.tri_src.assign(n, 0u);
+  uint32_t level_base = 0, tri_before = 0, depth = 0;
+  while (!frontier_a.empty()) {
+    const uint32_t n_f = (uint32_t)frontier_a.size();
+    std::vector<Collected> col(n_f);
+    word.assign(n_f, 0); scan.assign(n_f, 0);
+    uint64_t acc = 0;
+    for (uint32_t f = 0; f < n_f; f++) { word[f] = emit_collect(t, frontier_a[f], ep, col[f]); scan[f] = acc; acc += word[f]; }
+    frontier_b.assign((size_t)(acc & 0xFFFFFFFFull), 0u);
+    out.nodes.resize((size_t)(level_base + n_f) * 4 * CRT_NODE_STRIDE);
+    for (uint32_t f = 0; f < n_f; f++) {
+      const uint32_t inner_off = (uint32_t)(scan[f] & 0xFFFFFFFFull), tri_off = (uint32_t)(scan[f] >> 32);
+      emit_node(t, col[f], ep, level_base + f, level_base + n_f + inner_off, tri_before + tri_off, leaf_tri.data(), out.nodes.data(), frontier_b.data(), inner_off,
+                out.tri_src.data());
+    }
+    level_base += n_f; tri_before += (uint32_t)(acc >> 32);
+    frontier_a.swap(frontier_b);
+    depth++;
+  }
+  out.n_nodes = level_base; out.max_depth = depth;
 }
 
 }  // namespace crt

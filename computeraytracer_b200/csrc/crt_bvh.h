@@ -14,11 +14,23 @@ struct BvhResult {
   uint32_t n_nodes = 0;
   uint32_t max_depth = 0;          // depth of the wide tree
   float pad = 0.0f;
+  double build_ms = 0.0;
   float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};   // padded bounds of all triangles
 };
 
+// Builder settings (crt_params.bvh_tuning / bvh_prim_cost; tools/bvh_eval.py).  None of them can change a result.
+struct BvhOptions {
+  int bins = 32;                // SAH bins per axis (4 .. 256)
+  bool optimal_slots = false;   // exact child-slot assignment (dynamic programme over slot sets) instead of the greedy one
+  float prim_cost = 0.75f;      // SAH weight of a triangle test relative to a node visit in the Wide8 collapse
+};
+BvhOptions bvh_options(uint32_t bvh_tuning, float prim_cost);
+
 // prims: binding-8 bytes (80-byte records); tri_pos: positions of the category-2 records.
 // Deterministic: the result does not depend on the number of threads.
-void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n_threads, BvhResult& out);
+void build_bvh(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, int n_threads, const BvhOptions& opt, BvhResult& out);
+
+// The device build's algorithm run by loops on the host (validation of crt_bvh_ploc.h without a GPU; single-threaded).
+void build_bvh_ploc_host(const uint8_t* prims, const std::vector<uint32_t>& tri_pos, const BvhOptions& opt, BvhResult& out);
 
 }  // namespace crt

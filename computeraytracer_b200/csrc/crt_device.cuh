@@ -140,6 +140,22 @@ __device__ __forceinline__ float rnd(Rng& s) {
   return (float)(s.x & 0x00ffffffu) / 16777216.0f;
 }
 
+// ------------------------------------------------------------------------------------------------ work units
+// unit -> pixel: units enumerate a rank's 8x4-pixel tiles, 32 pixels each; under CRT_SHARD_TILES rank r owns the tiles with
+// tile_id % world == r (interleaved, because cost per tile is very uneven: sky against glass silhouettes)
+__device__ __forceinline__ bool unit_pixel_of(uint32_t unit, uint32_t rank, uint32_t world, bool tiles_sharded, uint32_t tiles_x, uint32_t W, uint32_t H,
+                                              uint32_t& px, uint32_t& py) {
+  uint32_t tile = unit >> 5;
+  const uint32_t l = unit & 31u;
+  if (tiles_sharded) tile = tile * world + rank;
+  px = (tile % tiles_x) * 8u + (l & 7u);
+  py = (tile / tiles_x) * 4u + (l >> 3);
+  return px < W && py < H;
+}
+__device__ __forceinline__ bool unit_pixel(const DevScene& sc, uint32_t unit, uint32_t& px, uint32_t& py) {
+  return unit_pixel_of(unit, sc.rank, sc.world, sc.shard_mode == CRT_SHARD_TILES && sc.world > 1, sc.tiles_x, sc.W, sc.H, px, py);
+}
+
 // ------------------------------------------------------------------------------------------------ intersection
 struct Hit {
   float t;        // context.t_max after the scan (CS:577); CRT_INFINITY_F when nothing was accepted

@@ -249,6 +249,66 @@ __global__ void resolve_kernel(const float4* __restrict__ acc, uint32_t* __restr
   fb[i] = resolve_pixel(a.x, a.y, a.z, sample, exposure);
 }
 
+// ------------------------------------------------------------------------------------------------ multi-GPU combine
+// Tile gather (one process per GPU, NCCL): a rank packs the accumulator entries of the tiles it owns -- W*H*16/world bytes --
+// into a contiguous send buffer in unit order; the destination unpacks each peer's buffer into the combined accumulator.
+__global__ void pack_tiles_kernel(const float4* __restrict__ acc, float4* __restrict__ out, uint32_t n_units, uint32_t rank, uint32_t world,
+                                  uint32_t tiles_x, uint32_t W, uint32_t H) {
+  const uint32_t unit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= n_units) return;
+  uint32_t px, py;
+  const bool in = unit_pixel_of(unit, rank, world, true, tiles_x, W, H, px, py);
+  out[unit] = in ? acc[px + py * W] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
+__global__ void unpack_tiles_kernel(const float4* __restrict__ in, float4* __restrict__ acc, uint32_t n_units, uint32_t rank, uint32_t world,
+                                    uint32_t tiles_x, uint32_t W, uint32_t H) {
+  const uint32_t unit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= n_units) return;
+  uint32_t px, py;
+  if (unit_pixel_of(unit, rank, world, true, tiles_x, W, H, px, py)) acc[px + py * W] = in[unit];
+}
+
+// Fused combine of a single-process group (crt_create_multi): member 0 reads the members' accumulators through NVLink peer
+// pointers, sums the split-spp partials in rank order (or, for tiles, takes each pixel from the one member that owns it: W*H*16
+// bytes cross the links in total, W*H*16/world per member), and writes the combined accumulator and the tone-mapped
+// framebuffer (CS:109-115) in the same pass.
+__global__ void combine_peers_kernel(const CombinePeers peers, float4* __restrict__ comb, uint32_t* __restrict__ fb, uint32_t W, uint32_t H,
+                                     uint32_t tiles_x, uint32_t sample, float exposure) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= W * H) return;
+  float4 a;
+  if (peers.tiles) {
+    const uint32_t px = i % W, py = i / W;
+    const uint32_t tile = (py >> 2) * tiles_x + (px >> 3);
+    a = peers.acc[tile % peers.n][i];
+  } else {
+    a = peers.acc[0][i];
+    for (uint32_t r = 1; r < peers.n; r++) {
+      const float4 b = peers.acc[r][i];
+      a.x += b.x; a.y += b.y; a.z += b.z;
+    }
+  }
+  comb[i] = a;
+  fb[i] = resolve_pixel(a.x, a.y, a.z, sample, exposure);
+}
+
+// FP32 pipe microbenchmark ("measure an FP32 FMA microbenchmark in the bench run"): 8 independent FFMA chains
+// per thread (explicit fmaf: the library is built with -fmad=false), 2 flops per FFMA.  The measured rate is the yardstick for
+// the linear-list regime (configs 1-2), which is FP32/issue-bound, not HBM-bound.
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float* __restrict__ out, uint32_t iters, float a, float b) {
+  float x0 = threadIdx.x, x1 = x0 + 1.0f, x2 = x0 + 2.0f, x3 = x0 + 3.0f, x4 = x0 + 4.0f, x5 = x0 + 5.0f, x6 = x0 + 6.0f, x7 = x0 + 7.0f;
+  for (uint32_t i = 0; i < iters; i++) {
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+      x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+    }
+  }
+  const float s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;   // never true: keeps the chains alive
+}
+
 // detmath probe: the CUDA build of include/crt_detmath.h, compared bit for bit with the oracle's build
 __global__ void detmath_kernel(const float* __restrict__ x, uint32_t n, float* s, float* c, float* e, float* p) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -314,6 +374,27 @@ cudaError_t launch_trace_rays(const DevScene& sc, const float4* rays, const uint
 
 cudaError_t launch_resolve(const float4* acc, uint32_t* fb, uint32_t n, uint32_t sample, float exposure, cudaStream_t s) {
   if (n) resolve_kernel<<<(n + 255) / 256, 256, 0, s>>>(acc, fb, n, sample, exposure);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pack_tiles(const float4* acc, float4* out, uint32_t n_units, uint32_t rank, uint32_t world, uint32_t tiles_x, uint32_t W,
+                              uint32_t H, cudaStream_t s) {
+  if (n_units) pack_tiles_kernel<<<(n_units + 255) / 256, 256, 0, s>>>(acc, out, n_units, rank, world, tiles_x, W, H);
+  return cudaGetLastError();
+}
+cudaError_t launch_unpack_tiles(const float4* in, float4* acc, uint32_t n_units, uint32_t rank, uint32_t world, uint32_t tiles_x, uint32_t W,
+                                uint32_t H, cudaStream_t s) {
+  if (n_units) unpack_tiles_kernel<<<(n_units + 255) / 256, 256, 0, s>>>(in, acc, n_units, rank, world, tiles_x, W, H);
+  return cudaGetLastError();
+}
+cudaError_t launch_combine_peers(const CombinePeers& peers, float4* comb, uint32_t* fb, uint32_t W, uint32_t H, uint32_t tiles_x,
+                                 uint32_t sample, float exposure, cudaStream_t s) {
+  combine_peers_kernel<<<(W * H + 255) / 256, 256, 0, s>>>(peers, comb, fb, W, H, tiles_x, sample, exposure);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_fp32_peak(float* out, int grid, uint32_t iters, cudaStream_t s) {
+  fp32_peak_kernel<<<grid, 256, 0, s>>>(out, iters, 0.999f, 0.001f);
   return cudaGetLastError();
 }
 

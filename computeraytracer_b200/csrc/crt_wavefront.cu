@@ -58,16 +58,6 @@ __device__ __forceinline__ void rec_stu(const WfState& w, uint32_t slot, int wor
 #define WF_FLAG_DEAD 8u               // Russian roulette ended the path; only the pending contribution is outstanding
 #define WF_FLAG_LZERO 0x800u          // (bit 31 of the packed word) L is still 0 and its sector has not been written for this path
 
-// unit -> pixel: units enumerate this rank's 8x4 tiles, 32 pixels each (the megakernel's unit order)
-__device__ __forceinline__ bool unit_pixel(const DevScene& sc, uint32_t unit, uint32_t& px, uint32_t& py) {
-  uint32_t tile = unit >> 5;
-  const uint32_t l = unit & 31u;
-  if (sc.shard_mode == CRT_SHARD_TILES && sc.world > 1) tile = tile * sc.world + sc.rank;
-  px = (tile % sc.tiles_x) * 8u + (l & 7u);
-  py = (tile / sc.tiles_x) * 4u + (l >> 3);
-  return px < sc.W && py < sc.H;
-}
-
 __device__ __forceinline__ void wf_load(const WfState& w, uint32_t slot, PathState& ps, Rng& rng, uint32_t& wid, uint32_t& flags) {
   const float4 a = rec_ld(w, slot, WF_R_S0), b = rec_ld(w, slot, WF_R_S1);
   ps.o = v3(a); ps.pdf = a.w;
@@ -259,14 +249,13 @@ __device__ __forceinline__ int wf_bounce(const DevScene& sc, const float* __rest
 }
 
 // end of a path: spectral_to_xyz (CS:105) into the staging buffer at (sample ordinal, pixel); wf_accumulate adds in order
-__device__ __forceinline__ void wf_finish(const DevScene& sc, const WfChunk& ck, const float* __restrict__ cie, float4 L, uint32_t lam0, uint32_t wid) {
+__device__ __forceinline__ void wf_finish(const DevScene& /*sc*/, const WfChunk& ck, const float* __restrict__ cie, float4 L, uint32_t lam0, uint32_t wid) {
   uint32_t lam[4];
   wavelengths(lam0, lam);
   const V3 xyz = spectral_to_xyz(cie, L, lam);
-  const uint32_t j = wid / ck.n_units;
-  uint32_t px, py;
-  unit_pixel(sc, wid - j * ck.n_units, px, py);
-  ck.stage[(size_t)j * ck.n_pixels + (px + py * sc.W)] = make_float4(xyz.x, xyz.y, xyz.z, 0.0f);   // CS:107
+  // staged by work item = (sample ordinal, unit): a rank that owns 1/world of the tiles stages 1/world of the bytes, and a
+  // warp's 32 units (one 8x4 tile) are 512 contiguous bytes for wf_accumulate
+  ck.stage[wid] = make_float4(xyz.x, xyz.y, xyz.z, 0.0f);   // CS:107
 }
 
 // the pending NEE contribution of a slot, as the reference would have added it (CS:187 with CS:400 or CS:407)
@@ -510,11 +499,17 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
 // different phases (ncu: ~17 of 32 active), but these kernels wait on memory and on dependent arithmetic rather than on
 // issue slots, and the fused form makes one pass over a slot's record per bounce instead of up to two.
 template <bool STATS>
-__global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(const __grid_constant__ DevScene sc, const WfState w, const WfChunk ck, uint32_t it,
+__global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(const __grid_constant__ DevScene sc, const WfState w, uint32_t it_arg,
                                                      uint32_t routed, unsigned long long* __restrict__ counters) {
   extern __shared__ float s_tables[];
+  __shared__ WfChunk s_ck;   // the chunk (written by wf_begin) is read from shared memory where it is used: in registers it
+  __shared__ uint32_t s_it;  // cost wf_logic 44 bytes of spills, as a kernel parameter it would pin the graph loop to one chunk
+  if (threadIdx.x == 0) { s_ck = w.ctl->ck; s_it = it_arg == CRT_WF_IT_DEVICE ? w.ctl->it : it_arg; }   // graph loop: the iteration lives on the device
+  __syncthreads();
   const float *spectra, *cie;
   wf_tables(sc, w, s_tables, spectra, cie);
+  const WfChunk& ck = s_ck;
+  const uint32_t it = s_it;
   // Routed forms (`routed` = WF_LIVE_ROUTED or WF_LIVE_CLASS): the live slots arrive in two lists -- the finish list (extension ray missed, or only an NEE
   // answer was outstanding: these lanes finish the path and start the next one) padded to whole warps, then the bounce
   // list (surface hit: these lanes shade) -- so the lanes of a warp are in the same phase of this kernel.  wf_emit and
@@ -648,26 +643,24 @@ __device__ __forceinline__ void done_add(DoneBuf& b, bool pred, uint32_t slot, u
 // slowest ray.  Every trip of the loop is one triangle test for the lanes that have triangles pending, then one node
 // step (fetch an 8-wide node, test its child boxes) for the lanes whose triangle group is empty by then.  (Measured:
 // triangles first is 4 % faster than nodes first; batching the triangle tests until 6..24 lanes have some is 35-85 %
-// slower -- the kernel lives on overlapping the node and triangle fetches of different lanes; prefetch.global.L1 of the
+// slower -- the kernel lives on overlapping the node and triangle fetches of different lanes; letting a lane keep walking nodes
+// while it holds one postponed triangle group until 4 / 8 / 12 lanes hold triangles is 3-4 % slower although it needs fewer
+// instructions, and taking 32 queue entries per atomic with a refill threshold of 2 / 4 is 4 % slower / equal
+// (profiles/r02a_traverse_schedule_ab.txt: the kernel waits for its fetches, not for issue slots); prefetch.global.L1 of the
 // next node or triangle changes nothing; one merged fetch phase per trip -- triangle lanes and node lanes load through the
 // same registers and the warp waits once -- is equal on mesh1m and 5 % slower on the 10M soup.)  Arithmetic per node and per triangle is wide_node / wide_tri
 // (crt_device.cuh), the same code the megakernel and the trace-rays hook run.
 #ifndef WF_SSTACK
 #define WF_SSTACK 8          // entries of a lane's traversal stack kept in shared memory, the rest in local memory (0 -> 8: wf_traverse -1.5 % on mesh1m, -2.6 % on soup10m; 5 = 8)
 #endif
-#ifndef WF_BATCH_FETCH
-#define WF_BATCH_FETCH 0     // > 0: a warp takes this many BVH-queue entries per atomic (see wf_traverse's refill)
-#endif
-#ifndef WF_POSTPONE
-#define WF_POSTPONE 0        // > 0: postponed leaves, the triangle step waits for this many lanes (see wf_traverse)
-#endif
 #ifndef WF_REFILL_MIN
 #define WF_REFILL_MIN 8
 #endif
 template <bool STATS, bool ROUTE>
-__global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(const __grid_constant__ DevScene sc, const WfState w, uint32_t it,
+__global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(const __grid_constant__ DevScene sc, const WfState w, uint32_t it_arg,
                                                         uint32_t fix_class, unsigned long long* __restrict__ counters) {
   __shared__ uint32_t s_done[WF_BLOCK / 32][2][64];
+  const uint32_t it = it_arg == CRT_WF_IT_DEVICE ? w.ctl->it : it_arg;
   const uint32_t n_ext = w.iter[it].n_bvh;
   const uint32_t n = n_ext + w.iter[it].n_shadow;   // one fetch cursor over both queues: extension rays first
   if (n == 0) return;
@@ -695,17 +688,9 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
 #define WF_PUSH(g) do { stack[sp++] = (g); } while (0)
 #define WF_POP(g) do { (g) = stack[--sp]; } while (0)
 #endif
-#if WF_POSTPONE
-  __shared__ uint2 s_post[WF_BLOCK];   // a lane's postponed triangle group
-  bool walked = false;                 // the lane's ray has no node left to visit
-  s_post[threadIdx.x] = make_uint2(0u, 0u);
-#endif
   int sp = 0;
   uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);   // node group and triangle group of the lane's ray (crt_device.cuh)
   bool have = false, exhausted = false, anyhit = false, lin_miss = false;
-#if WF_BATCH_FETCH
-  uint32_t qnext = 0, qend = 0;   // the warp's current share of the queue (warp-uniform)
-#endif
   uint32_t slot = 0, exclude = CRT_MAX_U32, light_prim = 0;
   V3 d = v3(0.0f, 0.0f, 1.0f);
   WideRay r = wide_ray(v3(0.0f, 0.0f, 0.0f), d);
@@ -720,37 +705,15 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     uint32_t mask = __ballot_sync(0xffffffffu, need);
     if (__popc(mask) < WF_REFILL_MIN && __ballot_sync(0xffffffffu, have) != 0u) mask = 0u;
     if (mask) {
-#if WF_BATCH_FETCH
-      // Batched fetch (tuning, off by default): the warp takes WF_BATCH_FETCH queue entries with one atomic and hands them
-      // to its lanes as they fall idle, so a refill is an index computation plus the new rays' loads and the threshold
-      // WF_REFILL_MIN can come down (tools/wide8_sim.c prices today's refill event at ~90 step-instructions).
-      if (qnext >= qend) {   // warp-uniform: the warp's share is used up
-        uint32_t b0 = 0;
-        if (lane == 0) b0 = atomicAdd(fetch, (uint32_t)WF_BATCH_FETCH);
-        b0 = __shfl_sync(0xffffffffu, b0, 0);
-        qnext = b0 < n ? b0 : n;
-        qend = b0 + (uint32_t)WF_BATCH_FETCH < n ? b0 + (uint32_t)WF_BATCH_FETCH : n;
-      }
-      const uint32_t base = qnext;
-      const uint32_t q_end = qend;
-      qnext = base + (uint32_t)__popc(mask) < qend ? base + (uint32_t)__popc(mask) : qend;
-#else
       uint32_t base = 0;
       const uint32_t leader = __ffs(mask) - 1u;
       if (lane == leader) base = atomicAdd(fetch, (uint32_t)__popc(mask));
       base = __shfl_sync(0xffffffffu, base, leader);
-#endif
       if (need) {
         const uint32_t q = base + __popc(mask & ((1u << lane) - 1u));
-#if WF_BATCH_FETCH
-        if (q >= q_end) {
-          if (q_end == n) exhausted = true;   // the queue itself is used up; otherwise the lane waits for the warp's next batch
-        } else {
-#else
         if (q >= n) {
           exhausted = true;
         } else {
-#endif
           anyhit = q >= n_ext;
           slot = anyhit ? w.shadow_list[q - n_ext] : queue[q];
           const float4 a = rec_ld(w, slot, WF_R_S0);
@@ -774,62 +737,13 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
           T = make_uint2(0u, 0u);
           sp = 0;
           have = true;
-#if WF_POSTPONE
-          s_post[threadIdx.x] = make_uint2(0u, 0u); walked = !r.valid;
-#endif
           ray_nodes = ray_tris = 0;
         }
       }
     }
-#if WF_BATCH_FETCH
-    if (__ballot_sync(0xffffffffu, have) == 0u) {
-      if (__ballot_sync(0xffffffffu, !exhausted) == 0u) break;
-      continue;   // lanes wait for the warp's next batch
-    }
-#else
     if (__ballot_sync(0xffffffffu, have) == 0u) break;
-#endif
     // ---- triangle step: one triangle for every lane that has some left
     bool done = false;
-#if WF_POSTPONE
-    // Postponed leaves (tuning, off by default; modelled in tools/wide8_sim.c: node steps 22 -> 25 lanes, 7-9 % fewer
-    // step instructions per ray): a lane keeps walking nodes while it holds ONE postponed triangle group, and the
-    // triangle step runs only when WF_POSTPONE lanes hold triangles, or a lane has found a second group, or a lane has
-    // triangles left and no node, or nobody has node work.  Every triangle of a hit leaf is still tested against the
-    // best hit known at that moment, so results are the same; postponed triangles cannot shorten the ray in time, so a
-    // few more nodes are visited.
-    {
-      uint2 P = s_post[threadIdx.x];   // the postponed group (y == 0: none)
-      const bool both = P.y != 0u && T.y != 0u;
-      const bool tri_have = have && (T.y | P.y) != 0u;
-      const uint32_t want = (uint32_t)__popc(__ballot_sync(0xffffffffu, tri_have));
-      const bool run_tri = want != 0u && (want >= WF_POSTPONE || __ballot_sync(0xffffffffu, have && (both || (tri_have && walked))) != 0u ||
-                                          __ballot_sync(0xffffffffu, have && !walked && !both) == 0u);
-      if (run_tri && tri_have) {
-        const bool from_p = P.y != 0u;
-        uint2 S = from_p ? P : T;
-        if (STATS) ray_tris++;
-        if (wide_tri<STATS>(tris, S, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
-        if (from_p) P = S; else T = S;
-      }
-      if (have && !done && !(P.y != 0u && T.y != 0u)) {
-        if (T.y != 0u) { P = T; T.y = 0u; }
-        if (!walked && !(G.y & CRT_WIDE_HITS)) {
-          if (sp == 0) walked = true;
-          else WF_POP(G);
-        }
-        if (!walked) {
-          const uint32_t node = wide_pop_child(G, r.octinv);
-          if (G.y & CRT_WIDE_HITS) WF_PUSH(G);
-          wide_node<STATS>(nodes, node, r, one, t_min, h.t, G, T, st);
-          if (STATS) ray_nodes++;
-        } else if (P.y == 0u) {
-          done = true;   // no node and no triangle left
-        }
-      }
-      s_post[threadIdx.x] = P;
-    }
-#else
     if (have && T.y != 0u) {
       if (STATS) ray_tris++;
       if (wide_tri<STATS>(tris, T, r.o, d, exclude, t_min, anyhit, h, st)) done = true;
@@ -848,7 +762,6 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
         if (STATS) ray_nodes++;
       }
     }
-#endif
     // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
     //      to the next iteration's shade queue (surface) or finish queue (miss)
     const bool fin_ext = done && !anyhit;
@@ -900,7 +813,9 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
 // Tiles reach the lists in arrival order, which is close enough to slot order for wf_logic's record stream to stay
 // sequential in memory.
 #define WF_PART_PER_THREAD 16
-__global__ void __launch_bounds__(256) wf_partition(const WfState w, uint32_t n_slots, uint32_t it) {
+__global__ void __launch_bounds__(256) wf_partition(const WfState w, uint32_t it_arg) {
+  const uint32_t it = it_arg == CRT_WF_IT_DEVICE ? w.ctl->it : it_arg;
+  const uint32_t n_slots = w.ctl->ck.n_slots;
   __shared__ uint32_t s_warp[2][8];
   __shared__ uint32_t s_base[2], s_tot[2];
   __shared__ uint32_t s_out[2][256 * WF_PART_PER_THREAD];   // the tile's entries by class, then copied out coalesced
@@ -957,6 +872,26 @@ __global__ void __launch_bounds__(256) wf_partition(const WfState w, uint32_t n_
   }
 }
 
+// Start of a chunk: the control block takes the chunk and iteration 0.  (The per-iteration counters and the work counter are
+// cleared by a memset on the same stream.)
+__global__ void wf_begin(const WfState w, const WfChunk ck) {
+  w.ctl->ck = ck;
+  w.ctl->it = 0u;
+  w.ctl->error = 0u;
+}
+
+// End of an iteration of the graph loop: advance the iteration and tell the WHILE node whether any slot is still live (the
+// lists of iteration it + 1 are complete: wf_logic / wf_traverse pushed them or wf_partition built them).
+__global__ void wf_next(const WfState w, cudaGraphConditionalHandle loop, uint32_t kernels_per_iter) {
+  const uint32_t it = w.ctl->it + 1u;
+  w.ctl->it = it;
+  w.ctl->iters_total++;
+  w.ctl->launches_total += kernels_per_iter;
+  bool more = (w.iter[it].n_bounce | w.iter[it].n_finish) != 0u;
+  if (more && it + 2u >= CRT_WF_MAX_ITERS) { more = false; w.ctl->error = 1u; }   // cannot happen: the host sizes chunks for the worst case
+  cudaGraphSetConditional(loop, more ? 1u : 0u);
+}
+
 // acc += sample_1, += sample_2, ... in frame order (CS:108 over the chunk's frames), then the epilogue of
 // main (CS:109-115) with the frame counter after the chunk.
 __global__ void wf_accumulate(const __grid_constant__ DevScene sc, const WfChunk ck, float4* __restrict__ acc, uint32_t* __restrict__ fb,
@@ -968,7 +903,7 @@ __global__ void wf_accumulate(const __grid_constant__ DevScene sc, const WfChunk
   const uint32_t pix = px + py * sc.W;
   float4 a = acc[pix];
   for (uint32_t j = 0; j < ck.n_samples; j++) {
-    const float4 v = ck.stage[(size_t)j * ck.n_pixels + pix];
+    const float4 v = ck.stage[(size_t)j * ck.n_units + unit];
     a.x += v.x; a.y += v.y; a.z += v.z;
   }
   acc[pix] = a;
@@ -995,10 +930,15 @@ cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* sh
 #undef CRT_WF_CFG
 }
 
-cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
+cudaError_t launch_wf_begin(const WfState& w, const WfChunk& ck, cudaStream_t s) {
+  wf_begin<<<1, 1, 0, s>>>(w, ck);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s) {
-  if (stats) wf_logic<true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, ck, it, live_mode, counters);
-  else wf_logic<false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, ck, it, live_mode, counters);
+  if (stats) wf_logic<true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
+  else wf_logic<false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
   return cudaGetLastError();
 }
 
@@ -1029,9 +969,64 @@ cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats,
   return cudaGetLastError();
 }
 
-cudaError_t launch_wf_partition(const WfState& w, uint32_t n_slots, int grid, uint32_t it, cudaStream_t s) {
-  wf_partition<<<grid, 256, 0, s>>>(w, n_slots, it);
+cudaError_t launch_wf_partition(const WfState& w, int grid, uint32_t it, cudaStream_t s) {
+  wf_partition<<<grid, 256, 0, s>>>(w, it);
   return cudaGetLastError();
+}
+
+// WHILE (live slots) { wf_logic; [wf_traverse;] [wf_partition;] wf_next } as one CUDA graph: the host enqueues a chunk with one
+// launch and never waits for it; the loop ends on the device (cudaGraphSetConditional in wf_next).
+cudaError_t wf_graph_build(const DevScene& sc, const WfState& w, bool stats, uint32_t logic_mode, uint32_t live_mode, int grid_l, int grid_t,
+                           int grid_p, size_t smem, unsigned long long* counters, uint32_t kernels_per_iter, cudaGraph_t* graph, cudaGraphExec_t* exec) {
+  cudaError_t e;
+  cudaGraph_t g = nullptr;
+  if ((e = cudaGraphCreate(&g, 0)) != cudaSuccess) return e;
+  cudaGraphConditionalHandle loop;
+  if ((e = cudaGraphConditionalHandleCreate(&loop, g, 1u, cudaGraphCondAssignDefault)) != cudaSuccess) { cudaGraphDestroy(g); return e; }
+  cudaGraphNodeParams cp = {};
+  cp.type = cudaGraphNodeTypeConditional;
+  cp.conditional.handle = loop;
+  cp.conditional.type = cudaGraphCondTypeWhile;
+  cp.conditional.size = 1;
+  cudaGraphNode_t cond;
+  if ((e = cudaGraphAddNode(&cond, g, nullptr, 0, &cp)) != cudaSuccess) { cudaGraphDestroy(g); return e; }
+  cudaGraph_t body = cp.conditional.phGraph_out[0];
+  uint32_t it = CRT_WF_IT_DEVICE;
+  cudaGraphNode_t prev = nullptr, node = nullptr;
+  auto add = [&](void* func, dim3 grid, dim3 block, size_t shmem, void** args) -> cudaError_t {
+    cudaKernelNodeParams kp = {};
+    kp.func = func; kp.gridDim = grid; kp.blockDim = block; kp.sharedMemBytes = (unsigned)shmem; kp.kernelParams = args; kp.extra = nullptr;
+    const cudaError_t rc = cudaGraphAddKernelNode(&node, body, prev ? &prev : nullptr, prev ? 1 : 0, &kp);
+    prev = node;
+    return rc;
+  };
+  {
+    void* args[] = {(void*)&sc, (void*)&w, &it, &logic_mode, &counters};
+    e = add(stats ? (void*)wf_logic<true> : (void*)wf_logic<false>, dim3(grid_l), dim3(WF_LOGIC_BLOCK), smem, args);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); return e; }
+  }
+  if (sc.n_tri) {
+    uint32_t fix_class = live_mode == 2 ? 1u : 0u;
+    void* args[] = {(void*)&sc, (void*)&w, &it, &fix_class, &counters};
+    void* f = live_mode == 1 ? (stats ? (void*)wf_traverse<true, true> : (void*)wf_traverse<false, true>)
+                             : (stats ? (void*)wf_traverse<true, false> : (void*)wf_traverse<false, false>);
+    e = add(f, dim3(grid_t), dim3(WF_BLOCK), 0, args);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); return e; }
+  }
+  if (live_mode == 2) {
+    void* args[] = {(void*)&w, &it};
+    e = add((void*)wf_partition, dim3(grid_p), dim3(256), 0, args);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); return e; }
+  }
+  {
+    void* args[] = {(void*)&w, &loop, &kernels_per_iter};
+    e = add((void*)wf_next, dim3(1), dim3(1), 0, args);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); return e; }
+  }
+  cudaGraphExec_t x = nullptr;
+  if ((e = cudaGraphInstantiate(&x, g, 0)) != cudaSuccess) { cudaGraphDestroy(g); return e; }
+  *graph = g; *exec = x;
+  return cudaSuccess;
 }
 
 cudaError_t launch_wf_accumulate(const DevScene& sc, const WfChunk& ck, float4* acc, uint32_t* fb, uint32_t sample_after, cudaStream_t s) {

@@ -22,7 +22,31 @@ struct WfIter {
 #define CRT_WF_REC_WORDS 10     // 16-byte words per slot record (160 bytes = 5 DRAM sectors); layout in crt_wavefront.cu
 #define WF_REC_WORDS CRT_WF_REC_WORDS
 
+// One chunk of frames rendered as a wavefront.
+struct WfChunk {
+  uint32_t n_units;     // pixels (8x4-tile order) this rank owns
+  uint32_t n_slots;     // size of the path-slot pool working on the chunk
+  uint32_t n_samples;   // samples of the chunk this rank renders (ordinals 0 .. n_samples-1)
+  uint32_t s_first;     // frame number of ordinal 0
+  uint32_t s_stride;    // frame number step between ordinals (world size under split-spp, else 1)
+  uint32_t n_pixels;    // W * H
+  float4* stage;        // [n_samples][n_units]: XYZ of each finished path, indexed by work item, summed in order by wf_accumulate
+};
+
+// Device-resident control block of the running chunk: written by wf_begin, advanced by wf_next.  The iteration kernels read
+// the chunk from here, and -- when their `it` argument is CRT_WF_IT_DEVICE -- the iteration number too, so that the whole
+// iteration loop can run as a CUDA-graph WHILE node without the host (crt_wavefront.cu, wf_graph_build).
+struct WfCtl {
+  uint32_t it;          // current iteration
+  uint32_t error;       // 1: the per-iteration counters ran out (CRT_WF_MAX_ITERS)
+  uint32_t iters_total; // iterations run since the context was created (diagnostics)
+  uint32_t launches_total; // kernels the graph loop has launched
+  WfChunk ck;
+};
+#define CRT_WF_IT_DEVICE 0xFFFFFFFFu
+
 struct WfState {
+  WfCtl* ctl;          // control block (device memory)
   float4* rec;         // [slots * WF_REC_WORDS] path state, one contiguous record per slot
   uint32_t* bounce[2]; // shade queue of this / the next iteration
   uint32_t* finish[2]; // finish queue of this / the next iteration
@@ -37,24 +61,17 @@ struct WfState {
   float4* slow;        // [1 + 3 * CRT_WF_SLOW_RAYS]: word 0 = count, then (origin, iteration), (direction, nodes), (exclude, anyhit, slot, triangles)
 };
 
-// One chunk of frames rendered as a wavefront.
-struct WfChunk {
-  uint32_t n_units;     // pixels (8x4-tile order) this rank owns
-  uint32_t n_slots;     // size of the path-slot pool working on the chunk
-  uint32_t n_samples;   // samples of the chunk this rank renders (ordinals 0 .. n_samples-1)
-  uint32_t s_first;     // frame number of ordinal 0
-  uint32_t s_stride;    // frame number step between ordinals (world size under split-spp, else 1)
-  uint32_t n_pixels;    // W * H: stride of the staging buffer
-  float4* stage;        // [n_samples][n_pixels]: XYZ of each finished path, summed in order by wf_accumulate
-};
 
 namespace crt {
 size_t wf_tables_bytes(const DevScene& sc);
 // resident blocks per SM of wf_logic / wf_shade / wf_regen / wf_traverse
 cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* shade_blocks_per_sm, int* regen_blocks_per_sm,
                       int* trav_blocks_per_sm);
+// start of a chunk: the control block takes the chunk, iteration 0
+cudaError_t launch_wf_begin(const WfState& w, const WfChunk& ck, cudaStream_t s);
 // live_mode: 0 one live list, 1 routed lists (pushed by wf_logic and wf_traverse), 2 class bytes + wf_partition (crt_wavefront.cu)
-cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
+// it: the iteration, or CRT_WF_IT_DEVICE (read it from the control block)
+cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_shade(const DevScene& sc, const WfState& w, const WfChunk& ck, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s);
@@ -62,6 +79,10 @@ cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk&
                             unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, bool fix_class, int grid, uint32_t it,
                                unsigned long long* counters, cudaStream_t s);
-cudaError_t launch_wf_partition(const WfState& w, uint32_t n_slots, int grid, uint32_t it, cudaStream_t s);
+cudaError_t launch_wf_partition(const WfState& w, int grid, uint32_t it, cudaStream_t s);
 cudaError_t launch_wf_accumulate(const DevScene& sc, const WfChunk& ck, float4* acc, uint32_t* fb, uint32_t sample_after, cudaStream_t s);
+// The iteration loop of one chunk as a CUDA graph: WHILE (live slots) { wf_logic; wf_traverse; wf_partition; wf_next }.  The graph
+// depends on the scene (a kernel parameter), the buffers and the launch shapes, not on the chunk: build once, launch per chunk.
+cudaError_t wf_graph_build(const DevScene& sc, const WfState& w, bool stats, uint32_t logic_mode, uint32_t live_mode, int grid_l, int grid_t,
+                           int grid_p, size_t smem, unsigned long long* counters, uint32_t kernels_per_iter, cudaGraph_t* graph, cudaGraphExec_t* exec);
 }  // namespace crt

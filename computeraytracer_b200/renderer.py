@@ -36,8 +36,14 @@ KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
 FLAG_STATS, FLAG_KERNEL_TIMES, FLAG_WF_SPLIT = 1, 2, 4
 KERNEL_CLASSES = ["wf_logic", "wf_traverse", "wf_accumulate", "pt_megakernel", "wf_regen", "wf_shade", "wf_partition"]
 
+# crt_params.wf_tuning / bvh_tuning bits (include/crt.h)
+WF_LIVE_ONE_LIST, WF_LIVE_ROUTED, WF_LIVE_CLASS = 1, 2, 3
+WF_DEFER_OFF, WF_DEFER_ON, WF_HOST_LOOP = 4, 8, 16
+BVH_EXACT_SLOTS, BVH_BUILDER_HOST_SAH, BVH_BUILDER_DEVICE = 0x200, 0x400, 0x800
+COMM_ID_BYTES = 128
+
 STATUS = {0: "CRT_OK", 1: "CRT_ERR_ARG", 2: "CRT_ERR_BINDING", 3: "CRT_ERR_SIZE", 4: "CRT_ERR_STATE",
-          5: "CRT_ERR_CUDA", 6: "CRT_ERR_OOM", 7: "CRT_ERR_NODEVICE"}
+          5: "CRT_ERR_CUDA", 6: "CRT_ERR_OOM", 7: "CRT_ERR_NODEVICE", 8: "CRT_ERR_NCCL"}
 
 
 class CrtError(RuntimeError):
@@ -49,7 +55,8 @@ class CrtError(RuntimeError):
 class Params(C.Structure):
     """``struct crt_params`` (include/crt.h)."""
     _fields_ = [("max_depth", C.c_uint32), ("grid_size", C.c_uint32), ("t_min", C.c_float), ("exposure", C.c_float),
-                ("kernel", C.c_uint32), ("frames_per_launch", C.c_uint32), ("flags", C.c_uint32), ("wf_slots", C.c_uint32), ("reserved", C.c_uint32 * 4)]
+                ("kernel", C.c_uint32), ("frames_per_launch", C.c_uint32), ("flags", C.c_uint32), ("wf_slots", C.c_uint32),
+                ("wf_tuning", C.c_uint32), ("bvh_tuning", C.c_uint32), ("bvh_prim_cost", C.c_float), ("slow_ray_nodes", C.c_uint32)]
 
 
 _lib = None
@@ -93,6 +100,15 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.crt_get_kernel_times.argtypes = [vp, vp, vp, sz]
     lib.crt_scene_stats.argtypes = [vp, vp, sz]
     lib.crt_test_detmath.argtypes = [vp, vp, sz, vp, vp, vp, vp]
+    lib.crt_measure_fp32_tflops.argtypes = [vp, C.POINTER(C.c_double)]
+    lib.crt_create_multi.argtypes = [C.POINTER(C.c_int), C.c_int, u32, C.POINTER(vp)]
+    lib.crt_comm_unique_id.argtypes = [vp, sz]
+    lib.crt_comm_init.argtypes = [vp, vp, sz, u32, u32, u32]
+    lib.crt_comm_destroy.argtypes = [vp]
+    lib.crt_combine.argtypes = [vp, u32]
+    lib.crt_last_combine.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_uint64)]
+    lib.crt_read_bvh.argtypes = [vp, vp, sz, vp, sz, vp, vp]
+    lib.crt_host_build_bvh.argtypes = [vp, sz, C.c_int, vp, sz, vp, sz, vp, vp, u32, C.c_float]
     if path == LIB_PATH:
         _lib = lib
     return lib
@@ -107,16 +123,23 @@ def default_params(**kw) -> Params:
 
 
 class Renderer:
-    """One libcrt context on one GPU."""
+    """One libcrt context: one GPU (``Renderer(device)``) or, with ``devices=[...]``, a single-process group of GPUs
+    (``crt_create_multi``) that shards tiles or frames and combines them on its first member at readback."""
 
-    def __init__(self, device: int = 0, lib: Optional[C.CDLL] = None):
+    def __init__(self, device: int = 0, lib: Optional[C.CDLL] = None, devices=None, shard_mode: int = SHARD_SPLIT_SPP):
         self.lib = lib or load_library()
         h = C.c_void_p()
-        rc = self.lib.crt_create(device, C.byref(h))
+        if devices is not None:
+            arr = (C.c_int * len(devices))(*devices)
+            rc = self.lib.crt_create_multi(arr, len(devices), shard_mode, C.byref(h))
+            device = devices[0] if len(devices) else 0
+        else:
+            rc = self.lib.crt_create(device, C.byref(h))
         if rc:
-            raise CrtError(rc, f"crt_create(device={device}) failed -- libcrt needs a B200 (sm_100); there is no CPU fallback")
+            raise CrtError(rc, f"crt_create(device={devices if devices is not None else device}) failed -- libcrt needs a B200 (sm_100); there is no CPU fallback")
         self.h = h
         self.device = device
+        self.devices = list(devices) if devices is not None else [device]
         self.width = self.height = 0
 
     # ---- lifetime
@@ -183,6 +206,31 @@ class Renderer:
 
     def set_shard(self, rank: int, world: int, mode: int) -> None:
         self._ck(self.lib.crt_set_shard(self.h, rank, world, mode))
+
+    # ---- multi-GPU, one process per GPU: NCCL behind the C ABI (the host layer only carries the 128-byte id)
+    def comm_unique_id(self) -> bytes:
+        buf = C.create_string_buffer(COMM_ID_BYTES)
+        rc = self.lib.crt_comm_unique_id(buf, COMM_ID_BYTES)
+        if rc:
+            raise CrtError(rc, "crt_comm_unique_id failed (is libnccl.so.2 loadable?)")
+        return buf.raw
+
+    def comm_init(self, comm_id: bytes, rank: int, world: int, mode: int) -> None:
+        self._ck(self.lib.crt_comm_init(self.h, comm_id, len(comm_id), rank, world, mode))
+
+    def comm_destroy(self) -> None:
+        self._ck(self.lib.crt_comm_destroy(self.h))
+
+    def combine(self, dst: int = 0) -> None:
+        """Collective: split-spp partial sums are reduced, owned tiles gathered, to rank ``dst`` (a group: its member 0),
+        which also rebuilds binding 0.  Repeatable; asynchronous on the context's stream."""
+        self._ck(self.lib.crt_combine(self.h, dst))
+
+    def last_combine(self):
+        """(device ms of the most recent combine, bytes this rank sent)"""
+        ms, nb = C.c_float(), C.c_uint64()
+        self._ck(self.lib.crt_last_combine(self.h, C.byref(ms), C.byref(nb)))
+        return float(ms.value), int(nb.value)
 
     def reset(self) -> None:
         self._ck(self.lib.crt_reset(self.h))
@@ -265,10 +313,29 @@ class Renderer:
         self._ck(self.lib.crt_reset_counters(self.h))
 
     def scene_stats(self) -> dict:
-        out = np.zeros(8, dtype=np.uint64)
-        self._ck(self.lib.crt_scene_stats(self.h, out.ctypes.data, 8))
-        keys = ["n_prims", "n_linear", "n_triangles", "bvh_nodes", "bvh_bytes", "tri_bytes", "build_us", "bvh_depth"]
-        return {k: int(out[i]) for i, k in enumerate(keys)}
+        out = np.zeros(10, dtype=np.uint64)
+        self._ck(self.lib.crt_scene_stats(self.h, out.ctypes.data, 10))
+        keys = ["n_prims", "n_linear", "n_triangles", "bvh_nodes", "bvh_bytes", "tri_bytes", "build_us", "bvh_depth", "tree_us"]
+        d = {k: int(out[i]) for i, k in enumerate(keys)}
+        d["builder"] = {0: "none", 1: "host_sah", 2: "device_ploc"}[int(out[9]) & 0xFF]
+        d["shadow_closest"] = bool(int(out[9]) & 0x100)
+        return d
+
+    def measure_fp32_tflops(self) -> float:
+        """Measured FP32 FMA rate of the device (TFLOP/s): the yardstick of the linear-list (FP32-bound) regime."""
+        v = C.c_double()
+        self._ck(self.lib.crt_measure_fp32_tflops(self.h, C.byref(v)))
+        return float(v.value)
+
+    def read_bvh(self):
+        """Test hook: (nodes uint32[n_nodes, 20], primitive index per leaf-order slot, info, bounds) of the resident tree."""
+        info = np.zeros(4, dtype=np.uint64)
+        bounds = np.zeros(7, dtype=np.float32)
+        self._ck(self.lib.crt_read_bvh(self.h, None, 0, None, 0, info.ctypes.data, bounds.ctypes.data))
+        nodes = np.zeros((int(info[0]), int(info[3])), dtype=np.uint32)
+        idx = np.zeros(int(info[1]), dtype=np.uint32)
+        self._ck(self.lib.crt_read_bvh(self.h, nodes.ctypes.data, nodes.size, idx.ctypes.data, idx.size, info.ctypes.data, bounds.ctypes.data))
+        return nodes, idx, info, bounds
 
     def test_detmath(self, x: np.ndarray):
         x = np.ascontiguousarray(x, dtype=np.float32)

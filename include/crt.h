@@ -50,7 +50,8 @@ enum crt_status {
   CRT_ERR_STATE = 4,    /* a required binding (4..8) has not been set yet              */
   CRT_ERR_CUDA = 5,     /* CUDA runtime error; text in crt_last_error                  */
   CRT_ERR_OOM = 6,      /* host or device allocation failed                            */
-  CRT_ERR_NODEVICE = 7  /* no CUDA device / wrong architecture: there is no CPU fallback */
+  CRT_ERR_NODEVICE = 7, /* no CUDA device / wrong architecture: there is no CPU fallback */
+  CRT_ERR_NCCL = 8      /* NCCL missing (libnccl.so.2 not loadable) or an NCCL call failed; text in crt_last_error */
 };
 
 enum crt_shard_mode {
@@ -78,8 +79,36 @@ typedef struct crt_params {
   uint32_t flags;       /* CRT_FLAG_* bits (instrumentation; results never depend on them)     */
   uint32_t wf_slots;    /* wavefront kernel: path slots in flight (0 = library default, 64 Mi);
                            results never depend on it                                           */
-  uint32_t reserved[4];
+  /* Tuning words (all 0 = library defaults; none of them can change a result -- tests/test_gpu_parity.py runs the
+     non-default settings against the oracle).  They replace what round 1 read from the process environment. */
+  uint32_t wf_tuning;      /* CRT_WF_* bits below                                                   */
+  uint32_t bvh_tuning;     /* bits 0-8: SAH bins per axis (0 = 32); CRT_BVH_EXACT_SLOTS; CRT_BVH_BUILDER_* */
+  float    bvh_prim_cost;  /* SAH weight of a triangle test in the Wide8 collapse (0 = 0.75)        */
+  uint32_t slow_ray_nodes; /* diagnostics, with CRT_FLAG_STATS: log rays visiting >= this many nodes */
 } crt_params;
+
+/* wf_tuning: how wf_logic's live slots reach the next iteration ... */
+#define CRT_WF_LIVE_DEFAULT 0u      /* linear-list scenes: routed lists; scenes with triangles: class bytes + wf_partition */
+#define CRT_WF_LIVE_ONE_LIST 1u
+#define CRT_WF_LIVE_ROUTED 2u
+#define CRT_WF_LIVE_CLASS 3u
+#define CRT_WF_LIVE_MASK 3u
+/* ... whether a path that ends in a bounce warp is finished by the next iteration's finish warps ... */
+#define CRT_WF_DEFER_DEFAULT 0u     /* on for scenes with triangles */
+#define CRT_WF_DEFER_OFF 4u
+#define CRT_WF_DEFER_ON 8u
+#define CRT_WF_DEFER_MASK 12u
+/* ... and who runs the iteration loop: by default a CUDA-graph WHILE node on the device (crt_dispatch_frames never waits for
+ * the GPU); with this bit the host launches every iteration and reads the live count back at check points (the round-1 form;
+ * CRT_FLAG_KERNEL_TIMES and CRT_FLAG_WF_SPLIT imply it). */
+#define CRT_WF_HOST_LOOP 16u
+/* bvh_tuning */
+#define CRT_BVH_BINS_MASK 0x1FFu
+#define CRT_BVH_EXACT_SLOTS 0x200u
+#define CRT_BVH_BUILDER_AUTO 0u        /* device LBVH build when the scene has >= 32768 triangles, host SAH below */
+#define CRT_BVH_BUILDER_HOST_SAH 0x400u /* binned-SAH BVH2 on the host cores + SAH-optimal Wide8 collapse (best tree, slow build) */
+#define CRT_BVH_BUILDER_DEVICE 0x800u   /* Morton-sorted LBVH + Wide8 collapse on the GPU (fast build) */
+#define CRT_BVH_BUILDER_MASK 0xC00u
 
 #define CRT_FLAG_STATS 1u        /* detailed device counters (separate, slower kernel variants)   */
 #define CRT_FLAG_KERNEL_TIMES 2u /* CUDA events between hot-path launches: crt_get_kernel_times   */
@@ -139,8 +168,34 @@ CRT_API void crt_default_params(crt_params* p);
 CRT_API int crt_set_params(crt_ctx* ctx, const crt_params* p);
 CRT_API int crt_get_params(crt_ctx* ctx, crt_params* p);
 
-/* Multi-GPU (new; the reference is single-device).  One context per rank/GPU. */
+/* ---- Multi-GPU (new; the reference is single-device: one adapter, one device, MJ:8-9).  The scene is replicated, pixels
+ * (CRT_SHARD_TILES) or frames (CRT_SHARD_SPLIT_SPP) are sharded, and nothing is exchanged while rendering; the one exchange
+ * step is crt_combine at readback.  Two ways to run it:
+ *
+ *  (a) one process, n GPUs -- what a single Node.js process does: crt_create_multi returns ONE context that owns a member
+ *      context per device.  Every call below works on it: bindings/params/reset are replicated, crt_dispatch_frames runs all
+ *      members, crt_read_binding(0|1) combines first and returns the combined image of member 0, counters are summed.
+ *      crt_combine on such a context is one fused kernel on member 0 that reads the other members' accumulators through
+ *      NVLink peer pointers, sums them in rank order (deterministic) and writes the combined accumulator and the tone-mapped
+ *      framebuffer -- no staging copy, no separate resolve pass.
+ *  (b) one process per GPU (torchrun, MPI): each process creates its own context with crt_create and joins a communicator
+ *      with crt_comm_init; the host layer only has to carry the 128-byte id from rank 0 to the others.  crt_combine is then
+ *      ncclReduce(SUM, f32, W*H*4) to `dst` for split-spp, and for tiles a grouped ncclSend/ncclRecv of the OWNED tiles only
+ *      (W*H*16/world bytes per rank), unpacked on `dst`.  NCCL is loaded at run time (dlopen of libnccl.so.2).
+ *
+ * crt_combine is repeatable: the ranks' partial sums stay partial (split-spp reduces into a separate combined buffer on
+ * `dst`; a tile gather overwrites, never adds), so frames / combine / frames / combine gives the same image as one render.
+ * After crt_combine, bindings 0 and 1 read on `dst` are the combined image until the next dispatch, reset or set_binding. */
 CRT_API int crt_set_shard(crt_ctx* ctx, uint32_t rank, uint32_t world, uint32_t mode);
+CRT_API int crt_create_multi(const int* devices, int n, uint32_t shard_mode, crt_ctx** out);
+#define CRT_COMM_ID_BYTES 128
+CRT_API int crt_comm_unique_id(void* id_bytes, size_t nbytes);   /* rank 0: ncclGetUniqueId */
+CRT_API int crt_comm_init(crt_ctx* ctx, const void* id_bytes, size_t nbytes, uint32_t rank, uint32_t world, uint32_t shard_mode);
+CRT_API int crt_comm_destroy(crt_ctx* ctx);
+/* Collective (every rank calls it with the same dst); asynchronous on the context's stream.  Device time of the most recent
+ * combine (ms, CUDA events around it) and the bytes this rank sent: crt_last_combine. */
+CRT_API int crt_combine(crt_ctx* ctx, uint32_t dst);
+CRT_API int crt_last_combine(crt_ctx* ctx, float* ms, uint64_t* bytes_sent);
 
 /* frame() (MJ:597-611): n times { UpdateVariables.main: sample++ (UpdateVariables.wgsl:3-8);
  * ComputeShader.main over ceil(W/8) x ceil(H/8) workgroups: one more sample per pixel }.
@@ -185,8 +240,9 @@ CRT_API int crt_reset_counters(crt_ctx* ctx);
 CRT_API int crt_get_kernel_times(crt_ctx* ctx, double* ms, uint64_t* launches, size_t n);
 
 /* Scene-upload statistics: out[0]=N primitives, [1]=patches+spheres (linear list),
- * [2]=triangles, [3]=BVH nodes, [4]=BVH bytes, [5]=triangle bytes, [6]=build microseconds,
- * [7]=max BVH depth. */
+ * [2]=triangles, [3]=BVH nodes, [4]=BVH bytes, [5]=triangle bytes, [6]=scene upload microseconds (repack + tree),
+ * [7]=max BVH depth, [8]=microseconds of the tree build alone, [9]=builder (0 no triangles, 1 host SAH, 2 device) |
+ * 0x100 when a light is a triangle (shadow rays need closest-hit: megakernel only). */
 CRT_API int crt_scene_stats(crt_ctx* ctx, uint64_t* out, size_t n);
 
 /* Test hook: the CUDA build of crt_detmath.h (sin, cos, exp, pow(x, 1/2.4)) on n inputs, compared bit
@@ -201,7 +257,16 @@ CRT_API int crt_test_detmath(crt_ctx* ctx, const float* x, size_t n, float* sin_
  * root box, then the padding.  tri_src[slot] = position in binding 8 of the triangle at leaf-order
  * slot `slot`.  The result does not depend on `threads`. */
 CRT_API int crt_host_build_bvh(const void* prims, size_t nbytes, int threads, uint32_t* nodes, size_t node_words,
-                               uint32_t* tri_src, size_t tri_cap, uint64_t* info, float* bounds);
+                               uint32_t* tri_src, size_t tri_cap, uint64_t* info, float* bounds, uint32_t bvh_tuning, float bvh_prim_cost);
+
+/* Test hook: the tree the context traverses, copied back from the device whichever builder made it: nodes in the Wide8
+ * layout and, per leaf-order slot, the primitive index (data4.w) of the triangle stored there.  info as above; nodes == NULL
+ * sizes the outputs. */
+CRT_API int crt_read_bvh(crt_ctx* ctx, uint32_t* nodes, size_t node_words, uint32_t* tri_index, size_t tri_cap, uint64_t* info, float* bounds);
+
+/* Bench hook: measured FP32 FMA throughput of the device in TFLOP/s (a microbenchmark of independent FFMA chains): the
+ * roofline denominator of the linear-list regime, which is FP32/issue-bound. */
+CRT_API int crt_measure_fp32_tflops(crt_ctx* ctx, double* tflops);
 
 CRT_API const char* crt_last_error(crt_ctx* ctx);
 CRT_API const char* crt_version(void);

@@ -330,7 +330,9 @@ static void scene_build_accel(orc_scene* sc) {
   if (nt) {
     /* box padding: covers the rounding of t, of the hit point and of the slab test */
     float ext = fmaxf(shi[0] - slo[0], fmaxf(shi[1] - slo[1], shi[2] - slo[2]));
-    float pad = fmaxf(ext, 1.0f) * (1.0f / 16384.0f);
+    float maxabs = 0.0f;   /* f32 rounds vertices and o - v0 to an ulp of the coordinate: the pad scales with it too */
+    for (int k = 0; k < 3; k++) maxabs = fmaxf(maxabs, fmaxf(fabsf(slo[k]), fabsf(shi[k])));
+    float pad = fmaxf(fmaxf(ext, maxabs), 1.0f) * (1.0f / 16384.0f);
     sc->nodes = (bvh_node*)malloc(sizeof(bvh_node) * (2 * (size_t)nt));
     bvh_build_rec(sc, it, 0, nt, pad);
     for (uint32_t i = 0; i < nt; i++) sc->tri_ids[i] = it[i].id;

@@ -378,20 +378,362 @@ def test_wavefront_pool_and_chunk_size_never_change_results(gpu, oracle, wf_slot
     assert cg == (int(cc[0]), int(cc[1]), int(cc[2]))
 
 
-@pytest.mark.parametrize("routed,defer", [(0, 0), (1, 0), (2, 0), (2, 1), (1, 1)])
+@pytest.mark.parametrize("host_loop", [0, 16], ids=["graph_loop", "host_loop"])
+@pytest.mark.parametrize("live,defer", [(1, 4), (2, 4), (3, 4), (3, 8), (2, 8)])
 @pytest.mark.parametrize("maker,kw", [(scenes.mesh_scene, dict(n_lon=64, n_lat=32)), (scenes.default_scene, {})])
-def test_wavefront_scheduling_forms_never_change_results(gpu, oracle, monkeypatch, maker, kw, routed, defer):
-    """How wf_logic's live slots reach the next iteration (0: one live list; 1: finish and bounce lists filled by wf_logic
-    and wf_traverse; 2: class bytes + wf_partition -- in 1 and 2 a warp's lanes are in one phase, and with `defer` a path
-    that ends in a bounce warp is finished by the next iteration's finish warps) decides which thread runs which
-    pixel-sample when, nothing else: accumulator, framebuffer and counters stay the oracle's.  A small pool forces many
-    rounds per slot."""
-    monkeypatch.setenv("CRT_WF_ROUTED", str(routed))
-    monkeypatch.setenv("CRT_WF_DEFER", str(defer))
+def test_wavefront_scheduling_forms_never_change_results(gpu, oracle, maker, kw, live, defer, host_loop):
+    """How wf_logic's live slots reach the next iteration (crt_params.wf_tuning: 1 one live list; 2 finish and bounce lists
+    filled by wf_logic and wf_traverse; 3 class bytes + wf_partition -- in 2 and 3 a warp's lanes are in one phase, and with
+    CRT_WF_DEFER_ON a path that ends in a bounce warp is finished by the next iteration's finish warps) and who runs the
+    iteration loop (the CUDA-graph WHILE node on the device, or the host) decide which thread runs which pixel-sample
+    when, nothing else: accumulator, framebuffer and counters stay the oracle's.  A small pool forces many rounds per slot."""
     ps = maker(96, 64, **kw)
     gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
-    acc, fb, cg = _render(gpu, 7, kernel=2, max_depth=8, wf_slots=2048, frames_per_launch=0)
+    acc, fb, cg = _render(gpu, 7, kernel=2, max_depth=8, wf_slots=2048, frames_per_launch=0, wf_tuning=live | defer | host_loop)
     acc_c, fb_c, cc = oracle.scene(ps, default_params(max_depth=8)).render(7)
     assert_radiance(acc, acc_c, 7)
     assert np.array_equal(fb, fb_c)
     assert cg == (int(cc[0]), int(cc[1]), int(cc[2]))
+
+
+def test_dispatch_returns_before_the_stream_drains(gpu):
+    """include/crt.h: crt_dispatch_frames is asynchronous on the context's stream.  The wavefront iteration loop ends on the
+    device (a CUDA-graph WHILE node), so the call only enqueues: it returns while the GPU is still rendering, and the
+    work is all there after crt_synchronize.  (Round 1 read the live count back inside the loop and blocked.)"""
+    import time
+    ps = scenes.mesh_scene(1280, 720, n_lon=256, n_lat=128)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    gpu.set_params(default_params(kernel=2)); gpu.reset(); gpu.reset_counters()
+    gpu.frame(48); gpu.synchronize()                      # warm-up at the same size: pool and staging allocations, graph instantiation
+    gpu.reset(); gpu.reset_counters()
+    t0 = time.perf_counter(); gpu.frame(48); t_call = time.perf_counter() - t0
+    t0 = time.perf_counter(); gpu.synchronize(); t_wait = time.perf_counter() - t0
+    c = gpu.counters()
+    assert c["paths"] == 1280 * 720 * 48 and gpu.sample == 48
+    assert t_wait > 4 * t_call, (t_call, t_wait)          # the call came back long before the frames were done
+    # the host-driven loop does block (that is what it is for: events between launches)
+    gpu.set_params(default_params(kernel=2, wf_tuning=16)); gpu.reset()
+    t0 = time.perf_counter(); gpu.frame(48); t_call_h = time.perf_counter() - t0
+    gpu.synchronize()
+    assert t_call_h > 10 * t_call, (t_call, t_call_h)
+    gpu.set_params(default_params())
+
+
+# ------------------------------------------------------------------------------------------------ builders
+def _tree_ok(gpu, ps):
+    """The tree that is resident on the device passes the builder invariants (tests/test_bvh_builder.py check_tree)."""
+    from tests.test_bvh_builder import check_tree
+    nodes, idx, info, bounds = gpu.read_bvh()
+    pos_of = {int(v): k for k, v in enumerate(ps.primitives["data4"][:, 3])}
+    src = np.array([pos_of[int(i)] for i in idx], dtype=np.uint32)
+    pad = max(float(np.max(bounds[3:6] - bounds[0:3])), float(np.max(np.abs(bounds[0:6]))), 1.0) / 32768.0 * 0.99
+    b = bounds.copy(); b[6] = pad      # (crt_read_bvh does not return the pad; this is its lower bound from the padded root box)
+    return check_tree(nodes, src, int(info[2]), b, ps.primitives)
+
+
+@pytest.mark.parametrize("builder", [0x400, 0x800], ids=["host_sah", "device_ploc"])
+@pytest.mark.parametrize("maker,kw", [(scenes.mesh_scene, dict(n_lon=128, n_lat=64)), (scenes.soup_scene, dict(n=30_000))])
+def test_builders_give_valid_trees_and_identical_hits(gpu, oracle, maker, kw, builder):
+    """Host binned-SAH build and device PLOC build: the resident tree satisfies the builder invariants, and hit index and t
+    equal the oracle's linear scan bit for bit (tree shape never changes a result)."""
+    ps = maker(64, 64, **kw)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0); gpu.set_params(default_params(bvh_tuning=builder))
+    st = gpu.scene_stats()
+    assert st["builder"] == ("host_sah" if builder == 0x400 else "device_ploc") and st["bvh_nodes"] > 0
+    n_tri, leaves = _tree_ok(gpu, ps)
+    assert n_tri == ps.primitives.size - 6
+    rays = scenes.camera_rays(ps, 20000, seed=9)
+    rng = np.random.default_rng(4)
+    exclude = rng.integers(0, ps.primitives.size, size=rays.shape[0]).astype(np.uint32)
+    sc = oracle.scene(ps)
+    for ex in (None, exclude):
+        gi, gt = gpu.trace_rays(rays, ex)
+        ci, ct, _ = sc.trace_rays(rays, ex)
+        assert np.array_equal(gi, ci) and np.array_equal(gt.view(np.uint32), ct.view(np.uint32))
+    acc, fb, cg = _render(gpu, 2, kernel=2, max_depth=8, bvh_tuning=builder)
+    acc_c, fb_c, cc = oracle.scene(ps, default_params(max_depth=8)).render(2)
+    assert_radiance(acc, acc_c, 2)
+    assert np.array_equal(fb, fb_c) and cg == (int(cc[0]), int(cc[1]), int(cc[2]))
+    gpu.set_params(default_params())
+
+
+def test_device_build_falls_back_when_the_tree_is_deeper_than_the_stack(gpu, oracle):
+    """300 nested triangles around one centroid: the agglomerative build chains them deeper than the 32-entry traversal stack,
+    so upload_scene takes the host SAH build (median splits bound its depth) -- and the hits are the linear scan's."""
+    base = np.array([[0, 0, 0], [3, 0, 0], [0, 3, 0]], dtype=np.float32) - np.array([1, 1, 0], dtype=np.float32)
+    same = np.repeat(base[None], 300, axis=0) * np.linspace(1, 2, 300, dtype=np.float32)[:, None, None] * 40.0 + np.array([278, 200, 280], dtype=np.float32)
+    ps = scenes._with_triangles(scenes.default_scene(32, 32), 6, same)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0); gpu.set_params(default_params(bvh_tuning=0x800))
+    st = gpu.scene_stats()
+    assert st["builder"] == "host_sah" and st["bvh_depth"] + 2 <= 32
+    rays = scenes.camera_rays(ps, 4000, seed=2)
+    gi, gt = gpu.trace_rays(rays)
+    ci, ct, _ = oracle.scene(ps).trace_rays(rays)
+    assert np.array_equal(gi, ci) and np.array_equal(gt.view(np.uint32), ct.view(np.uint32))
+    assert (gi >= 6).sum() > 100
+    gpu.set_params(default_params())
+
+
+@pytest.mark.parametrize("builder", [0x400, 0x800], ids=["host_sah", "device_ploc"])
+@pytest.mark.parametrize("shift", [3.0e3, 2.0e4])
+def test_mesh_far_from_the_origin_bvh_equals_linear_scan(gpu, oracle, builder, shift):
+    """the conservative-culling pad was tied to the mesh's extent only; at |coordinate| / extent above ~2^9 it fell
+    below one ulp of the coordinates and vanished, so rays near box faces could be culled where the linear scan accepts
+    them.  A mesh of extent ~3 translated by 1e3 .. 1e4 times its extent, rays starting next to it and far from it:
+    BVH == linear scan, index and t, bit for bit."""
+    tris = scenes.displaced_sphere_triangles(96, 48, seed=3, center=(0.0, 0.0, 0.0), radius=1.5)
+    tris = (tris.astype(np.float64) + np.array([shift, -shift * 0.5, 0.25 * shift])).astype(np.float32)
+    ps = scenes._with_triangles(scenes.default_scene(32, 32), 6, tris)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0); gpu.set_params(default_params(bvh_tuning=builder))
+    rng = np.random.default_rng(int(shift))
+    c = np.array([shift, -shift * 0.5, 0.25 * shift])
+    n = 30000
+    rays = np.zeros((n, 8), dtype=np.float32)
+    tgt = c + rng.normal(size=(n, 3)) * 0.9                       # aim into and around the mesh, many grazing its silhouette
+    org = np.where(rng.random((n, 1)) < 0.5, c + rng.normal(size=(n, 3)) * 4.0, rng.uniform(0, 555, size=(n, 3)))
+    d = tgt - org
+    rays[:, 0:3] = org; rays[:, 4:7] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    gi, gt = gpu.trace_rays(rays)
+    ci, ct, _ = oracle.scene(ps).trace_rays(rays)
+    assert (ci >= 6).sum() > 5000
+    assert np.array_equal(gi, ci) and np.array_equal(gt.view(np.uint32), ct.view(np.uint32))
+    gpu.set_params(default_params())
+
+
+def test_adversarial_rays_bit_exact_vs_linear_scan(gpu, oracle):
+    """SURVEY 7.2-8 / VERDICT r1: NaN components, +-0 and axis-parallel directions, origins on a patch (t == t_min region),
+    |n.d| just above / below the 1e-4 cut-off (CS:546), grazing sphere rays (CS:602-612), coincident triangles and rays in
+    a triangle's plane (CS:557, 566) -- hit index and t equal the oracle's linear scan bit for bit, on the reference's scene
+    and on a scene with a BVH (the Wide8 slab test clamps |1/d| and skips NaN rays precisely for these)."""
+    base = scenes.default_scene(32, 32)
+    tri = np.array([[[100, 100, 300], [200, 100, 300], [100, 200, 300]]] * 2 + [[[150, 50, 250], [150, 250, 250], [150, 50, 450]]], dtype=np.float32)
+    soup = scenes.soup_triangles(3000, seed=9)
+    ps_tri = scenes._with_triangles(base, 6, np.concatenate([tri, soup]))
+    rng = np.random.default_rng(12)
+    rows = []
+
+    def add(o, d):
+        rows.append(list(o) + [0.0] + list(d) + [0.0])
+
+    nan, inf = float("nan"), float("inf")
+    for k in range(3):                                             # NaN / inf in every component of origin and direction
+        for bad in (nan, inf, -inf):
+            o = [278.0, 273.0, -800.0]; d = [0.0, 0.0, 1.0]
+            o2 = list(o); o2[k] = bad; add(o2, d)
+            d2 = list(d); d2[k] = bad; add(o, d2)
+    for ax in range(3):                                            # axis-parallel, +0 / -0 in the other components
+        for sgn in (1.0, -1.0):
+            for z in (0.0, -0.0):
+                for _ in range(40):
+                    d = [z, z, z]; d[ax] = sgn
+                    add(rng.uniform(1, 554, 3), d)
+                    add([150.0, float(rng.uniform(50, 250)), float(rng.uniform(250, 450))][::1], d)   # some inside the plane x = 150 of a triangle
+    for _ in range(300):                                           # origins exactly on the walls / floor / the light's plane
+        p = rng.uniform(0, 555, 3); p[int(rng.integers(0, 3))] = float(rng.choice([0.0, 555.0]))
+        v = rng.normal(size=3); add(p, v / np.linalg.norm(v))
+    for eps in (0.99e-4, 1.0e-4, 1.01e-4, 0.5e-4, 2e-4, -0.99e-4, -1.01e-4):   # |n.d| around 0.0001 against the floor (n = +-y)
+        for _ in range(20):
+            phi = rng.uniform(0, 2 * np.pi); h = np.sqrt(1 - eps * eps)
+            add([float(rng.uniform(100, 400)), 0.5 if eps < 0 else 0.0005, float(rng.uniform(100, 400))], [h * np.cos(phi), eps, h * np.sin(phi)])
+    cs, r = np.array([190.0, 90.0, 190.0]), 90.0                   # grazing the spheres (disc ~ 0): aim at the silhouette +- ulps
+    for centre, rad in ((cs, r),):
+        for _ in range(300):
+            o = np.array([278.0, 273.0, -800.0])
+            to_c = centre - o; L = np.linalg.norm(to_c); u = to_c / L
+            perp = np.cross(u, rng.normal(size=3)); perp /= np.linalg.norm(perp)
+            sin_a = rad / L * (1.0 + rng.normal() * 2e-7)
+            dd = u * np.sqrt(max(0.0, 1 - sin_a * sin_a)) + perp * sin_a
+            add(o, dd / np.linalg.norm(dd))
+    for _ in range(200):                                           # rays through the coincident pair's edges and vertices
+        a, b = rng.random(2); e = rng.integers(0, 3)
+        p = [(100 + 100 * a, 100, 300), (100, 100 + 100 * a, 300), (100 + 100 * a, 200 - 100 * a, 300)][int(e)]
+        add([p[0], p[1], 0.0], [0.0, 0.0, 1.0])
+        add([p[0], p[1], 300.0 - 50.0 * b], [0.0, 0.0, 1.0])
+    rays = np.array(rows, dtype=np.float32)
+    for ps in (base, ps_tri):
+        gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+        n_prims = ps.primitives.size
+        sc = oracle.scene(ps)
+        for ex in (None, rng.integers(0, min(n_prims, 12), size=rays.shape[0]).astype(np.uint32)):
+            gi, gt = gpu.trace_rays(rays, ex)
+            ci, ct, _ = sc.trace_rays(rays, ex)
+            bad = np.nonzero((gi != ci) | (gt.view(np.uint32) != ct.view(np.uint32)))[0]
+            assert bad.size == 0, (bad[:5], rays[bad[:5]], gi[bad[:5]], ci[bad[:5]], gt[bad[:5]], ct[bad[:5]])
+        assert len(np.unique(ci)) >= 8
+    # the same rays as a render cannot be issued, but NaN-producing paths can: a 2-frame render of the triangle scene stays bit-exact
+    acc, fb, cg = _render(gpu, 2, kernel=2, max_depth=8)
+    acc_c, fb_c, cc = oracle.scene(ps_tri, default_params(max_depth=8)).render(2)
+    assert_radiance(acc, acc_c, 2)
+
+
+# ------------------------------------------------------------------------------------------------ single-process group
+@pytest.mark.parametrize("mode", [SHARD_TILES, SHARD_SPLIT_SPP], ids=["tiles", "split_spp"])
+@pytest.mark.parametrize("n", [2, 3])
+def test_group_on_one_device_combines_like_one_gpu(gpu, oracle, mode, n):
+    """crt_create_multi with the same device n times (a group's logic does not care where its members live): bindings are
+    replicated, frames sharded, crt_read_binding combines on member 0 with the fused peer kernel.  Tiles: bit-identical to
+    one context; split-spp: within the tolerance; frames / read / frames / read equals one uninterrupted render (the
+    combine is repeatable: partial sums stay partial)."""
+    ps = scenes.mesh_scene(100, 52, n_lon=64, n_lat=32)            # ragged edge tiles on both axes
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    want5, fb5, c5 = _render(gpu, 5, max_depth=8)
+    gpu.frame(4)
+    want9, fb9 = gpu.accumulator(), gpu.framebuffer()
+    with Renderer(devices=[0] * n, shard_mode=mode) as g:
+        g.set_scene(ps); g.set_params(max_depth=8); g.reset(); g.reset_counters()
+        g.frame(5)
+        a5, f5 = g.accumulator(), g.framebuffer()
+        c = g.counters()
+        assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == c5 and g.sample == 5
+        g.frame(4)
+        a9, f9 = g.accumulator(), g.framebuffer()
+        a9b = g.accumulator()                                       # reading twice combines twice: same image
+        ms, nbytes = g.last_combine()
+        assert np.array_equal(a9.view(np.uint32), a9b.view(np.uint32)) and g.sample == 9
+        if mode == SHARD_TILES:
+            assert np.array_equal(a5[..., :3].view(np.uint32), want5[..., :3].view(np.uint32)) and np.array_equal(f5, fb5)
+            assert np.array_equal(a9[..., :3].view(np.uint32), want9[..., :3].view(np.uint32)) and np.array_equal(f9, fb9)
+            assert 0 < nbytes < 100 * 52 * 16                       # the others' tiles only
+        else:
+            for got, want, spp in ((a5, want5, 5), (a9, want9, 9)):
+                mx, rmse = radiance_errors(got, want, spp)
+                assert mx <= MAX_ABS_TOL and rmse <= RMSE_TOL
+            assert int(np.abs(f9.astype(int) - fb9.astype(int)).max()) <= 1
+            assert nbytes == (n - 1) * 100 * 52 * 16
+        # resume on a group: the saved image goes back in, more frames, same as uninterrupted (tiles: bit-identical)
+        g.reset(); g.set_binding(1, a5); g.set_binding(2, np.array([5], dtype=np.uint32))
+        g.frame(4)
+        r9 = g.accumulator()
+        if mode == SHARD_TILES:
+            assert np.array_equal(r9[..., :3].view(np.uint32), want9[..., :3].view(np.uint32))
+        else:
+            mx, rmse = radiance_errors(r9, want9, 9)
+            assert mx <= MAX_ABS_TOL and rmse <= RMSE_TOL
+
+
+# ------------------------------------------------------------------------------------------------ two physical GPUs
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+def _nccl_worker(rank, world, mode, port, out_dir):
+    import os as _os
+    import sys as _sys
+    _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
+    _os.environ["MASTER_ADDR"] = "127.0.0.1"; _os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    from computeraytracer_b200 import multi
+    dist.init_process_group("gloo", rank=rank, world_size=world)       # carries the 128-byte id only; the data path is libcrt's NCCL
+    ps = scenes.mesh_scene(100, 52, n_lon=64, n_lat=32)
+    with Renderer(rank) as r:
+        r.set_scene(ps); r.set_params(max_depth=8)
+        multi.init(r, mode)
+        r.reset(); r.frame(5); r.combine(0)
+        if rank == 0:
+            np.save(_os.path.join(out_dir, "a5.npy"), r.accumulator()); np.save(_os.path.join(out_dir, "f5.npy"), r.framebuffer())
+        r.frame(4); r.combine(0); r.combine(0)                         # repeatable
+        ms, nbytes = r.last_combine()
+        if rank == 0:
+            np.save(_os.path.join(out_dir, "a9.npy"), r.accumulator()); np.save(_os.path.join(out_dir, "f9.npy"), r.framebuffer())
+        else:
+            np.save(_os.path.join(out_dir, f"sent_{rank}.npy"), np.array([nbytes], dtype=np.int64))
+        r.synchronize()
+        dist.barrier()
+        r.comm_destroy()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs two physical GPUs (gpurun --gpus 2)")
+@pytest.mark.parametrize("mode", [SHARD_TILES, SHARD_SPLIT_SPP], ids=["tiles", "split_spp"])
+def test_two_gpus_nccl_combine_behind_the_c_abi(gpu, tmp_path, mode):
+    """One process per GPU, crt_comm_init + crt_combine (NCCL inside libcrt): tiles gathered from two physical devices are
+    bit-identical to one GPU and only the owned tiles travel; split-spp reduces within the tolerance; repeatable."""
+    import os
+    import torch.multiprocessing as mp
+    ps = scenes.mesh_scene(100, 52, n_lon=64, n_lat=32)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    want5, fb5, _ = _render(gpu, 5, max_depth=8)
+    gpu.frame(4)
+    want9, fb9 = gpu.accumulator(), gpu.framebuffer()
+    mp.spawn(_nccl_worker, args=(2, mode, 29700 + os.getpid() % 1000 + mode, str(tmp_path)), nprocs=2, join=True)
+    a5, f5, a9, f9 = (np.load(tmp_path / f"{k}.npy") for k in ("a5", "f5", "a9", "f9"))
+    sent = int(np.load(tmp_path / "sent_1.npy")[0])
+    if mode == SHARD_TILES:
+        assert np.array_equal(a5[..., :3].view(np.uint32), want5[..., :3].view(np.uint32)) and np.array_equal(f5, fb5)
+        assert np.array_equal(a9[..., :3].view(np.uint32), want9[..., :3].view(np.uint32)) and np.array_equal(f9, fb9)
+        assert sent == ((13 * 13) // 2) * 32 * 16                   # rank 1 owns 84 of the 169 tiles: 84 x 32 x 16 bytes
+    else:
+        for got, want, spp in ((a5, want5, 5), (a9, want9, 9)):
+            mx, rmse = radiance_errors(got, want, spp)
+            assert mx <= MAX_ABS_TOL and rmse <= RMSE_TOL
+        assert sent == 100 * 52 * 16
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs two physical GPUs (gpurun --gpus 2)")
+@pytest.mark.parametrize("mode", [SHARD_TILES, SHARD_SPLIT_SPP], ids=["tiles", "split_spp"])
+def test_two_gpus_single_process_group(gpu, mode):
+    """crt_create_multi over two physical devices: the fused combine reads device 1's accumulator through a peer pointer."""
+    ps = scenes.mesh_scene(100, 52, n_lon=64, n_lat=32)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    want, fb, c1 = _render(gpu, 6, max_depth=8)
+    with Renderer(devices=[0, 1], shard_mode=mode) as g:
+        g.set_scene(ps); g.set_params(max_depth=8); g.reset(); g.reset_counters()
+        g.frame(6)
+        a, f = g.accumulator(), g.framebuffer()
+        c = g.counters()
+        assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == c1
+        if mode == SHARD_TILES:
+            assert np.array_equal(a[..., :3].view(np.uint32), want[..., :3].view(np.uint32)) and np.array_equal(f, fb)
+        else:
+            mx, rmse = radiance_errors(a, want, 6)
+            assert mx <= MAX_ABS_TOL and rmse <= RMSE_TOL
+
+
+# ------------------------------------------------------------------------------------------------ the other configs at full size
+def test_full_size_config2_cornell_1080p_64spp_tile_sample(gpu, oracle):
+    """BASELINE config 2 at its stated size (reference default scene, 1920x1080, 64 spp, max_depth 100): the tiles of one
+    shard of 64 are bit-identical to the oracle's render of the same tiles, the counters add up."""
+    ps = scenes.default_scene(1920, 1080)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    acc, fb, cg = _render(gpu, 64)
+    assert cg[0] == 1920 * 1080 * 64 and np.isfinite(acc[..., :3]).all()
+    cpu, fb_c, cc = oracle.scene(ps).render(64, rank=11, world=64, mode=SHARD_TILES)
+    own = cpu[..., :3].any(axis=-1)
+    assert own.sum() > 15000
+    assert np.array_equal(acc[own][:, :3].view(np.uint32), cpu[own][:, :3].view(np.uint32))
+    assert np.array_equal(fb[own], fb_c[own])
+
+
+def test_full_size_config4_mesh1m_4k_tile_sample(gpu, oracle):
+    """BASELINE config 4's image size (3840x2160) on the 1M-triangle scene: 1/256 of the tiles against the oracle's BVH path."""
+    ps = scenes.mesh_scene(3840, 2160)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    acc, fb, cg = _render(gpu, 2, kernel=2)
+    assert cg[0] == 3840 * 2160 * 2
+    cpu, _, cc = oracle.scene(ps, use_bvh=True).render(2, rank=77, world=256, mode=SHARD_TILES, want_fb=False)
+    own = cpu[..., :3].any(axis=-1)
+    assert own.sum() > 10000
+    assert np.array_equal(acc[own][:, :3].view(np.uint32), cpu[own][:, :3].view(np.uint32))
+
+
+def test_full_size_config5_soup10m_tile_sample(gpu, oracle):
+    """BASELINE config 5 at its stated size: 10,000,000 random triangles, max_depth 8, 1080p.  1/128 of the tiles against
+    the oracle's BVH path (itself pinned to its linear scan in tests/test_oracle_bvh.py), and 20K rays' hits."""
+    ps = scenes.soup_scene(1920, 1080)
+    assert ps.primitives.size == 10_000_006
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    acc, fb, cg = _render(gpu, 2, kernel=2, max_depth=8)
+    assert cg[0] == 1920 * 1080 * 2 and np.isfinite(acc[..., :3]).all()
+    sc = oracle.scene(ps, default_params(max_depth=8), use_bvh=True)
+    cpu, _, cc = sc.render(2, rank=5, world=128, mode=SHARD_TILES, want_fb=False)
+    own = cpu[..., :3].any(axis=-1)
+    assert own.sum() > 8000
+    assert np.array_equal(acc[own][:, :3].view(np.uint32), cpu[own][:, :3].view(np.uint32))
+    rays = scenes.camera_rays(ps, 20000, seed=3)
+    gi, gt = gpu.trace_rays(rays)
+    ci, ct, _ = sc.trace_rays(rays)
+    assert np.array_equal(gi, ci) and np.array_equal(gt.view(np.uint32), ct.view(np.uint32))

@@ -6,7 +6,9 @@ shadow rays towards the light -- and prints BVH nodes fetched and triangles test
 changes results (DESIGN.md "Conservative culling"), only these counts, which is what wf_traverse's time follows.
 On mesh1m it gives 8.4 nodes / 2.6 triangles per queued ray where the device counters say 9.4 / 3.1.
 
-    python tools/bvh_eval.py [mesh|soup] [n_lon or n_triangles] [ENV=VALUE ...]      e.g.  CRT_BVH_BINS=128
+    python tools/bvh_eval.py [mesh|soup] [n_lon or n_triangles] [KEY=VALUE ...]
+        BVH_TUNING=<crt_params.bvh_tuning>   e.g. 128 (bins) | 0x200 (exact slots) | 0x800 (the device build's PLOC algorithm)
+        BVH_PRIM_COST=<float>
     SIM_ORDER=1 python tools/bvh_eval.py ...     children visited by entry distance instead of by ray octant
 """
 import ctypes as C
@@ -42,16 +44,18 @@ def load_sim():
 
 
 def build_tree(prims):
-    lib = C.CDLL(build_libcrt())
+    lib = C.CDLL(os.environ.get("BVH_LIB") or build_libcrt())   # BVH_LIB: a host-only build of the builder (experiments)
     f = lib.crt_host_build_bvh
-    f.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    f.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float]
+    tuning = int(os.environ.get("BVH_TUNING", "0"), 0)
+    prim_cost = float(os.environ.get("BVH_PRIM_COST", "0"))
     raw = np.ascontiguousarray(prims).view(np.uint8)
     info = np.zeros(4, dtype=np.uint64); bounds = np.zeros(7, dtype=np.float32)
     t0 = time.perf_counter()
-    assert f(raw.ctypes.data, raw.size, os.cpu_count() or 1, None, 0, None, 0, info.ctypes.data, bounds.ctypes.data) == 0
+    assert f(raw.ctypes.data, raw.size, os.cpu_count() or 1, None, 0, None, 0, info.ctypes.data, bounds.ctypes.data, tuning, prim_cost) == 0
     dt = time.perf_counter() - t0
     nodes = np.zeros(int(info[0]) * int(info[3]), dtype=np.uint32); src = np.zeros(int(info[1]), dtype=np.uint32)
-    assert f(raw.ctypes.data, raw.size, os.cpu_count() or 1, nodes.ctypes.data, nodes.size, src.ctypes.data, src.size, info.ctypes.data, bounds.ctypes.data) == 0
+    assert f(raw.ctypes.data, raw.size, os.cpu_count() or 1, nodes.ctypes.data, nodes.size, src.ctypes.data, src.size, info.ctypes.data, bounds.ctypes.data, tuning, prim_cost) == 0
     return nodes, src, info, bounds, dt
 
 
@@ -154,7 +158,7 @@ def main():
         rows.append((f"shadow rays, depth {depth}", int(front.sum()), so.shape[0], scnt))
         o, d = P, cosine_dirs(n, rng)
     print(f"{kind}: {int(info[1]):,} triangles, {int(info[0]):,} wide nodes, depth {int(info[2])}, build {dt:.2f} s"
-          + "".join(f", {k}={v}" for k, v in os.environ.items() if k.startswith("CRT_BVH")))
+          + "".join(f", {k}={v}" for k, v in os.environ.items() if k.startswith("BVH_")))
     print(f"{'ray class':<28}{'rays':>9}{'queued':>9}{'nodes/queued':>14}{'tris/queued':>13}{'max nodes':>11}")
     for name, n_all, n_q, cnt in rows:
         if n_q:
