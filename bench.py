@@ -500,6 +500,23 @@ def run_b200(args):
             except Exception:
                 fp32 = None
             line["fp32_peak_tflops_measured"] = fp32
+            if st["n_triangles"] and args.bvh == "auto":
+                # the other builder on the same scene: the host binned-SAH tree is the quality option (crt_params.bvh_tuning), the
+                # device PLOC tree (AUTO's choice at this size) is the one that builds in milliseconds
+                other = BVH_BUILDER_HOST_SAH if st["builder"] == "device_ploc" else BVH_BUILDER_DEVICE
+                r.set_params(bvh_tuning=args.bvh_tuning | other)
+                t1 = time.perf_counter()
+                st2 = r.scene_stats(); r.synchronize()
+                setup2 = time.perf_counter() - t1
+                r.reset(); r.reset_counters()
+                time_steps(r, stream, torch, 2, frames, flush_buf, False)
+                ca = r.counters()
+                ms_o, _ = time_steps(r, stream, torch, 3, frames, flush_buf, False)
+                cb = r.counters()
+                line["other_bvh_builder"] = {"builder": st2["builder"], "bvh_build_ms": st2["tree_us"] / 1e3, "scene_upload_s": setup2,
+                                             "ms_per_step": sum(ms_o) / 3, "value": (cb["rays_ext"] - ca["rays_ext"]) / (sum(ms_o) * 1e-3) / 1e6,
+                                             "unit": UNIT, "bvh_nodes": st2["bvh_nodes"], "bvh_depth": st2["bvh_depth"]}
+                r.set_params(bvh_tuning=bvh_bits)
             if args.workload != "cornell":
                 from computeraytracer_b200 import scenes
                 r.set_scene(scenes.default_scene(args.width, args.height))

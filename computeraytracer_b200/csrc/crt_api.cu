@@ -458,7 +458,7 @@ int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
   CU(cudaMemset(w.ctl, 0, sizeof(WfCtl)));
   CU(cudaMemcpy(w.ctl, init, 16, cudaMemcpyHostToDevice));
   ctx->wf_slots = n_slots;
-  if (!ctx->wf_host_count) CU(cudaMallocHost(&ctx->wf_host_count, 8));
+  if (!ctx->wf_host_count) CU(cudaMallocHost(&ctx->wf_host_count, 16));
   return CRT_OK;
 }
 
@@ -489,6 +489,7 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   if (bl < 1 || bs < 1 || br < 1 || bt < 1) return fail(ctx, CRT_ERR_CUDA, "wavefront kernels do not fit on an SM");
   const int grid_l = ctx->sm_count * bl, grid_s = ctx->sm_count * bs, grid_r = ctx->sm_count * br, grid_t = ctx->sm_count * bt;
   const int grid_p = ctx->sm_count * 8;
+  const int grid_tail = ctx->sm_count * 2;   // wf_tail: a few thousand slots, one thread each (grid-stride)
   const bool split = (ctx->params.flags & CRT_FLAG_WF_SPLIT) != 0;   // three-kernel form (wf_shade / wf_regen) instead of wf_logic
   const bool host_loop = split || (ctx->params.flags & CRT_FLAG_KERNEL_TIMES) || (ctx->params.wf_tuning & CRT_WF_HOST_LOOP);
   // a path lives for at most max_depth+1 extension rays plus one pass for a trailing NEE answer
@@ -522,6 +523,9 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
   if (ctx->params.wf_tuning & CRT_WF_DEFER_MASK) defer = (ctx->params.wf_tuning & CRT_WF_DEFER_ON) ? 1u : 0u;
   const uint32_t logic_mode = live_mode | ((live_mode && defer) ? 0x100u : 0u);
   const uint32_t kernels_per_iter = 1u + (s.n_tri ? 1u : 0u) + (live_mode == 2 ? 1u : 0u) + 1u;   // graph loop, with wf_next
+  // the loop hands over to wf_tail when the chunk's work is used up and at most this many slots are live (crt_wavefront.cu)
+  const uint32_t tail_sel = (ctx->params.wf_tuning & CRT_WF_TAIL_MASK) >> CRT_WF_TAIL_SHIFT;
+  const uint32_t tail_max = split ? 0u : (tail_sel == 0 ? CRT_WF_TAIL_DEFAULT : (tail_sel == 31u ? 0u : (1u << (tail_sel - 1u))));
   uint32_t left = n;
   while (left) {
     const uint32_t k = left < chunk ? left : chunk;
@@ -558,22 +562,23 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       CU(crt::launch_wf_begin(ctx->wf, ck, ctx->stream));
       if (!host_loop) {
         // ---- the loop runs on the device
-        struct Key { DevScene sc; WfState w; uint32_t stats, logic_mode, live_mode; int gl, gt, gp; size_t smem; void* counters; };
+        struct Key { DevScene sc; WfState w; uint32_t stats, logic_mode, live_mode, tail_max; int gl, gt, gp; size_t smem; void* counters; };
         static_assert(std::is_trivially_copyable<Key>::value, "graph key");
         std::vector<uint8_t> key(sizeof(Key), 0);
         {
           Key kk; memset((void*)&kk, 0, sizeof(kk));
-          kk.sc = s; kk.w = ctx->wf; kk.stats = stats; kk.logic_mode = logic_mode; kk.live_mode = live_mode;
+          kk.sc = s; kk.w = ctx->wf; kk.stats = stats; kk.logic_mode = logic_mode; kk.live_mode = live_mode; kk.tail_max = tail_max;
           kk.gl = grid_l; kk.gt = grid_t; kk.gp = grid_p; kk.smem = smem; kk.counters = ctx->d_counters;
           memcpy(key.data(), &kk, sizeof(kk));
         }
         if (!ctx->wf_graph_exec || key != ctx->wf_graph_key) {
           drop_wf_graph(ctx);
-          CU(crt::wf_graph_build(s, ctx->wf, stats, logic_mode, live_mode, grid_l, grid_t, grid_p, smem, ctx->d_counters, kernels_per_iter,
+          CU(crt::wf_graph_build(s, ctx->wf, stats, logic_mode, live_mode, grid_l, grid_t, grid_p, smem, ctx->d_counters, kernels_per_iter, tail_max,
                                  &ctx->wf_graph, &ctx->wf_graph_exec));
           ctx->wf_graph_key = key;
         }
         CU(cudaGraphLaunch(ctx->wf_graph_exec, ctx->stream));
+        if (tail_max) { CU(crt::launch_wf_tail(s, ctx->wf, stats, live_mode, grid_tail, smem, CRT_WF_IT_DEVICE, ctx->d_counters, ctx->stream)); ctx->launches++; }
       } else {
         // ---- the host launches every iteration
         uint32_t it = 0;
@@ -607,9 +612,18 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
           if (it >= next_check) {
             CU(mark(ctx, -1));
             CU(cudaMemcpyAsync(ctx->wf_host_count, &ctx->wf.iter[it], 8, cudaMemcpyDeviceToHost, ctx->stream));   // n_bounce, n_finish
+            CU(cudaMemcpyAsync(ctx->wf_host_count + 2, ctx->wf.work, 4, cudaMemcpyDeviceToHost, ctx->stream));
             CU(cudaStreamSynchronize(ctx->stream));
-            if (ctx->wf_host_count[0] == 0 && ctx->wf_host_count[1] == 0) break;
-            next_check = it + 4;
+            const uint64_t live = (uint64_t)ctx->wf_host_count[0] + ctx->wf_host_count[1];
+            if (live == 0) break;
+            if (live <= tail_max && ctx->wf_host_count[2] >= total_work) {   // only a tail is left: wf_tail finishes it
+              CU(mark(ctx, CRT_KC_WF_TAIL));
+              CU(crt::launch_wf_tail(s, ctx->wf, stats, live_mode, grid_tail, smem, it, ctx->d_counters, ctx->stream));
+              CU(mark(ctx, -1));
+              ctx->launches++;
+              break;
+            }
+            next_check = it + (live <= 4ull * tail_max ? 1 : 4);
           }
           if (it + 2 >= CRT_WF_MAX_ITERS) return fail(ctx, CRT_ERR_STATE, "wavefront iteration limit reached");
         }

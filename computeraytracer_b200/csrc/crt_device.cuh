@@ -163,6 +163,19 @@ struct Hit {
   uint32_t ref;   // where the winner lives: linear-list slot, or CRT_TRI_REF | triangle slot
 };
 
+// `q = a / b; q < 0 || q > 1` (IEEE, round to nearest) without the division where the answer is the same bit for bit.
+// For 0 < b < 1e18:  a >= 0 gives q >= 0, and q > 1 exactly when a > b (a > b means a >= b + ulp, whose quotient rounds to at
+// least 1 + 2^-23; a <= b gives q <= 1; +-0 and NaN numerators fall out right: NaN compares false both ways, like the NaN
+// quotient);  a <= -1e-18 gives |q| >= 1e-36, a normal negative number, so q < 0.  What is left -- a in (-1e-18, 0), whose
+// quotient can underflow to -0 (which is NOT < 0), and b that is 0, negative, NaN or huge -- takes the real division.  The
+// patch test (CS:563-566) uses u and v for nothing but this comparison; two of its three divisions go away for every
+// ray that reaches it (ncu r01: IEEE divisions are 12 % of wf_logic's instructions).
+__device__ __forceinline__ bool outside_unit(float a, float b) {
+  if (b > 0.0f && b < 1e18f && !(a < 0.0f && a > -1e-18f)) return a < 0.0f || a > b;
+  const float q = a / b;
+  return q < 0.0f || q > 1.0f;
+}
+
 // ray_intersection for one linear-list entry, CS:520-632, sequential semantics (called in index order).
 // (The early exits stay: evaluating the patch test without them -- same tests, predicated -- made wf_logic 26 % slower;
 // whole warps leave at the exits often enough.)
@@ -179,9 +192,8 @@ __device__ __forceinline__ void test_lin(const LinPrim& p, uint32_t slot, V3 o, 
     float t = crt_div(dot(n, p0 - o), ndotd);        // CS:554
     if (t < t_min || t > h.t) return;                // CS:557
     V3 m = madd(o, t, d) - p0;                       // CS:561-562
-    float u = dot(m, v3(p.C)) / p.C.w;               // CS:563
-    float v = dot(m, v3(p.D)) / p.D.w;               // CS:564
-    if (u < 0.0f || u > 1.0f || v < 0.0f || v > 1.0f) return;  // CS:566
+    // CS:563-566: u = dot(m, e1) / dot(e1, e1), v likewise, rejected outside [0, 1] -- u and v are used for nothing else
+    if (outside_unit(dot(m, v3(p.C)), p.C.w) || outside_unit(dot(m, v3(p.D)), p.D.w)) return;
     h.t = t; h.idx = index; h.ref = slot;
   } else {
     V3 co = o - v3(p.A);                             // CS:597

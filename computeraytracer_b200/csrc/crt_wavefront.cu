@@ -609,6 +609,79 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
   wf_counts_flush<STATS>(lc, st, counters);
 }
 
+// wf_tail: the end of a chunk.  When the chunk has no work item left and only a few slots are still live, every further
+// iteration is three launches over a handful of warps -- the GPU idles through ~60 us per iteration for the 20-30
+// iterations the longest paths still need (Russian roulette has a long tail; a path in the glass sphere can go to
+// max_depth).  That tail was ~4 ms per chunk: 1 % of a 256-frame step, but 10 % of the 32 frames a rank renders per step when
+// eight GPUs share it, and more than half of a single-frame dispatch.  Instead the loop stops at that point (wf_next) and
+// this kernel runs each remaining slot's path to its end in one thread, megakernel style: the pending NEE answer and the
+// next closest hit are found inline (the same scan_linear / traverse / wf_bounce code, the same order of additions to L),
+// so the bits are those of the iterations it replaces.  Few lanes per warp are active here (that is why the megakernel
+// form loses on whole frames), which does not matter for the few thousand paths of a tail.
+template <bool STATS>
+__global__ void __launch_bounds__(WF_BLOCK) wf_tail(const __grid_constant__ DevScene sc, const WfState w, uint32_t it_arg, uint32_t routed,
+                                                    unsigned long long* __restrict__ counters) {
+  extern __shared__ float s_tables[];
+  const float *spectra, *cie;
+  wf_tables(sc, w, s_tables, spectra, cie);
+  const WfChunk ck = w.ctl->ck;
+  const uint32_t it = it_arg == CRT_WF_IT_DEVICE ? w.ctl->it : it_arg;
+  const uint32_t n_fin = (routed && it != 0) ? w.iter[it].n_finish : 0u;
+  const uint32_t n_cur = it == 0 ? 0u : n_fin + w.iter[it].n_bounce;   // (iteration 0 has no live list: nothing has started)
+  const uint32_t* __restrict__ cur = (it & 1u) ? w.bounce[1] : w.bounce[0];
+  const uint32_t* __restrict__ fin = (it & 1u) ? w.finish[1] : w.finish[0];
+  Stats st;
+  LogicCounts lc;
+  wf_counts_init(lc, st);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_cur; i += stride) {
+    const uint32_t slot = i < n_fin ? fin[i] : cur[i - n_fin];
+    PathState ps;
+    Rng rng;
+    uint32_t wid, flags;
+    wf_load(w, slot, ps, rng, wid, flags);
+    ps.L = wf_load_L(w, slot, flags);
+    if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // the outstanding NEE answer first (the reference's order)
+    if (!(flags & WF_FLAG_DEAD)) {
+      const float4 hv = rec_ld(w, slot, WF_R_H);
+      Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
+      for (;;) {
+        NeeQuery nee; nee.pending = false; nee.light_prim = 0;
+        uint32_t term = 0;
+        const int r = wf_bounce<STATS>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
+        if (STATS && r != 1) { lc.term_cnt[term - TERM_MISS]++; lc.depth_sum += ps.depth; }
+        if (nee.pending) {
+          // what wf_traverse answers for the shadow queue: does a triangle occlude the segment to the light?  (origin = the new
+          // ray's origin, exclude = the surface just hit)
+          Hit hs; hs.t = nee.t; hs.idx = nee.light_prim; hs.ref = 0;
+          traverse<true, STATS>(sc, ps.o, nee.d, ps.exclude, sc.t_min, hs, st);
+          float4 c = nee.c;
+          if (hs.idx != nee.light_prim) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407, as wf_pending does
+          ps.L.x += c.x; ps.L.y += c.y; ps.L.z += c.z; ps.L.w += c.w;
+          lc.n_bvh_rays++;
+        }
+        if (r != 1) break;
+        h = scan_linear<STATS>(sc, ps.o, ps.d, ps.exclude, st);   // the next extension ray: linear list, then the triangles
+        lc.n_ext++;
+        if (hits_root_box(sc, ps.o, ps.d, h.t)) { traverse<false, STATS>(sc, ps.o, ps.d, ps.exclude, sc.t_min, h, st); lc.n_bvh_rays++; }
+      }
+    } else if (STATS) {
+      // (a path Russian roulette ended earlier was counted when it ended)
+    }
+    wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
+    if (routed == WF_LIVE_CLASS) w.cls[slot] = (uint8_t)2;
+  }
+  wf_counts_flush<STATS>(lc, st, counters);
+  if (STATS) {   // BVH counters of the inline traversals
+    unsigned long long v[2] = {st.node_visits, st.tri_tests};
+    for (int k = 0; k < 2; k++) {
+      unsigned long long x = v[k];
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+      if ((threadIdx.x & 31u) == 0 && x) atomicAdd(&counters[CRT_CNT_NODE_VISITS + k], x);
+    }
+  }
+}
+
 // wf_traverse collects the slots of finished extension rays per warp in shared memory and appends them to the next
 // iteration's queues 32 at a time: one atomic (and one wait for it) per 32 rays instead of one per completion event.
 struct DoneBuf {
@@ -882,12 +955,16 @@ __global__ void wf_begin(const WfState w, const WfChunk ck) {
 
 // End of an iteration of the graph loop: advance the iteration and tell the WHILE node whether any slot is still live (the
 // lists of iteration it + 1 are complete: wf_logic / wf_traverse pushed them or wf_partition built them).
-__global__ void wf_next(const WfState w, cudaGraphConditionalHandle loop, uint32_t kernels_per_iter) {
+__global__ void wf_next(const WfState w, cudaGraphConditionalHandle loop, uint32_t kernels_per_iter, uint32_t tail_max) {
   const uint32_t it = w.ctl->it + 1u;
   w.ctl->it = it;
   w.ctl->iters_total++;
   w.ctl->launches_total += kernels_per_iter;
-  bool more = (w.iter[it].n_bounce | w.iter[it].n_finish) != 0u;
+  const uint32_t live = w.iter[it].n_bounce + w.iter[it].n_finish;
+  bool more = live != 0u;
+  // no work item left and only a tail of live slots: wf_tail finishes them (launched after the loop; it finds nothing when the
+  // loop ran to the end)
+  if (live <= tail_max && *w.work >= w.ctl->ck.n_units * w.ctl->ck.n_samples) more = false;
   if (more && it + 2u >= CRT_WF_MAX_ITERS) { more = false; w.ctl->error = 1u; }   // cannot happen: the host sizes chunks for the worst case
   cudaGraphSetConditional(loop, more ? 1u : 0u);
 }
@@ -924,6 +1001,7 @@ cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* sh
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<S>, WF_LOGIC_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(regen_blocks_per_sm, wf_regen<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
+  if ((e = cudaFuncSetAttribute(wf_tail<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;     \
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(trav_blocks_per_sm, wf_traverse<S, true>, WF_BLOCK, 0);
   if (stats) { CRT_WF_CFG(true) }
   CRT_WF_CFG(false)
@@ -969,6 +1047,13 @@ cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats,
   return cudaGetLastError();
 }
 
+cudaError_t launch_wf_tail(const DevScene& sc, const WfState& w, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
+                           unsigned long long* counters, cudaStream_t s) {
+  if (stats) wf_tail<true><<<grid, WF_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
+  else wf_tail<false><<<grid, WF_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_wf_partition(const WfState& w, int grid, uint32_t it, cudaStream_t s) {
   wf_partition<<<grid, 256, 0, s>>>(w, it);
   return cudaGetLastError();
@@ -977,7 +1062,7 @@ cudaError_t launch_wf_partition(const WfState& w, int grid, uint32_t it, cudaStr
 // WHILE (live slots) { wf_logic; [wf_traverse;] [wf_partition;] wf_next } as one CUDA graph: the host enqueues a chunk with one
 // launch and never waits for it; the loop ends on the device (cudaGraphSetConditional in wf_next).
 cudaError_t wf_graph_build(const DevScene& sc, const WfState& w, bool stats, uint32_t logic_mode, uint32_t live_mode, int grid_l, int grid_t,
-                           int grid_p, size_t smem, unsigned long long* counters, uint32_t kernels_per_iter, cudaGraph_t* graph, cudaGraphExec_t* exec) {
+                           int grid_p, size_t smem, unsigned long long* counters, uint32_t kernels_per_iter, uint32_t tail_max, cudaGraph_t* graph, cudaGraphExec_t* exec) {
   cudaError_t e;
   cudaGraph_t g = nullptr;
   if ((e = cudaGraphCreate(&g, 0)) != cudaSuccess) return e;
@@ -1019,7 +1104,7 @@ cudaError_t wf_graph_build(const DevScene& sc, const WfState& w, bool stats, uin
     if (e != cudaSuccess) { cudaGraphDestroy(g); return e; }
   }
   {
-    void* args[] = {(void*)&w, &loop, &kernels_per_iter};
+    void* args[] = {(void*)&w, &loop, &kernels_per_iter, &tail_max};
     e = add((void*)wf_next, dim3(1), dim3(1), 0, args);
     if (e != cudaSuccess) { cudaGraphDestroy(g); return e; }
   }

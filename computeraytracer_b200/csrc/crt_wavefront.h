@@ -80,9 +80,12 @@ cudaError_t launch_wf_regen(const DevScene& sc, const WfState& w, const WfChunk&
 cudaError_t launch_wf_traverse(const DevScene& sc, const WfState& w, bool stats, bool route, bool fix_class, int grid, uint32_t it,
                                unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_partition(const WfState& w, int grid, uint32_t it, cudaStream_t s);
+// the end of a chunk: every slot still live at iteration `it` runs its path to the end in one thread (it: as above)
+cudaError_t launch_wf_tail(const DevScene& sc, const WfState& w, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
+                           unsigned long long* counters, cudaStream_t s);
 cudaError_t launch_wf_accumulate(const DevScene& sc, const WfChunk& ck, float4* acc, uint32_t* fb, uint32_t sample_after, cudaStream_t s);
 // The iteration loop of one chunk as a CUDA graph: WHILE (live slots) { wf_logic; wf_traverse; wf_partition; wf_next }.  The graph
 // depends on the scene (a kernel parameter), the buffers and the launch shapes, not on the chunk: build once, launch per chunk.
 cudaError_t wf_graph_build(const DevScene& sc, const WfState& w, bool stats, uint32_t logic_mode, uint32_t live_mode, int grid_l, int grid_t,
-                           int grid_p, size_t smem, unsigned long long* counters, uint32_t kernels_per_iter, cudaGraph_t* graph, cudaGraphExec_t* exec);
+                           int grid_p, size_t smem, unsigned long long* counters, uint32_t kernels_per_iter, uint32_t tail_max, cudaGraph_t* graph, cudaGraphExec_t* exec);
 }  // namespace crt

@@ -34,11 +34,12 @@ COUNTER_NAMES = ["paths", "rays_ext", "rays_shadow", "prim_tests", "node_visits"
 SHARD_NONE, SHARD_TILES, SHARD_SPLIT_SPP = 0, 1, 2
 KERNEL_AUTO, KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1, 2
 FLAG_STATS, FLAG_KERNEL_TIMES, FLAG_WF_SPLIT = 1, 2, 4
-KERNEL_CLASSES = ["wf_logic", "wf_traverse", "wf_accumulate", "pt_megakernel", "wf_regen", "wf_shade", "wf_partition"]
+KERNEL_CLASSES = ["wf_logic", "wf_traverse", "wf_accumulate", "pt_megakernel", "wf_regen", "wf_shade", "wf_partition", "wf_tail"]
 
 # crt_params.wf_tuning / bvh_tuning bits (include/crt.h)
 WF_LIVE_ONE_LIST, WF_LIVE_ROUTED, WF_LIVE_CLASS = 1, 2, 3
 WF_DEFER_OFF, WF_DEFER_ON, WF_HOST_LOOP = 4, 8, 16
+WF_TAIL_SHIFT, WF_TAIL_OFF = 8, 31 << 8   # bits 8-12: v = 1..30 -> wf_tail takes over at <= 2^(v-1) live slots; 31: never
 BVH_EXACT_SLOTS, BVH_BUILDER_HOST_SAH, BVH_BUILDER_DEVICE = 0x200, 0x400, 0x800
 COMM_ID_BYTES = 128
 

@@ -102,6 +102,13 @@ typedef struct crt_params {
  * the GPU); with this bit the host launches every iteration and reads the live count back at check points (the round-1 form;
  * CRT_FLAG_KERNEL_TIMES and CRT_FLAG_WF_SPLIT imply it). */
 #define CRT_WF_HOST_LOOP 16u
+/* ... and when the iteration loop hands the chunk's last live slots to wf_tail (one thread runs a path to its end): bits
+ * 8-12 = 0: the default (at most CRT_WF_TAIL_DEFAULT live slots and no work item left), v = 1 .. 30: at most 2^(v-1) slots,
+ * 31: never (iterate until no slot is live, the round-1 form). */
+#define CRT_WF_TAIL_SHIFT 8
+#define CRT_WF_TAIL_MASK (31u << CRT_WF_TAIL_SHIFT)
+#define CRT_WF_TAIL_OFF (31u << CRT_WF_TAIL_SHIFT)
+#define CRT_WF_TAIL_DEFAULT 32768u
 /* bvh_tuning */
 #define CRT_BVH_BINS_MASK 0x1FFu
 #define CRT_BVH_EXACT_SLOTS 0x200u
@@ -124,7 +131,8 @@ enum crt_kernel_class {
   CRT_KC_WF_REGEN = 4,      /* wf_regen: finish ended paths, start new ones on free slots    */
   CRT_KC_WF_SHADE = 5,      /* wf_shade: one bounce per slot of the shade queue (split form) */
   CRT_KC_WF_PARTITION = 6,  /* wf_partition: bounce and finish lists from the slots' class bytes */
-  CRT_NUM_KERNEL_CLASSES = 7
+  CRT_KC_WF_TAIL = 7,       /* wf_tail: the chunk's last live slots, each path run to its end by one thread */
+  CRT_NUM_KERNEL_CLASSES = 8
 };
 
 #define CRT_NUM_COUNTERS 16

@@ -15,10 +15,17 @@
  *     reset(handle)                            zero accumulator, sample = 0             (main.js:298-311)
  *     dispatchFrames(handle, n)                n x frame()                              (main.js:597-611)
  *     readBinding(handle, n) -> ArrayBuffer    readback of bindings 0/1/2 (new)
- *     destroy(handle)
+ *     destroy(handle)                          frees the device memory now (pool, staging, scene), not at GC time
+ *   multi-GPU (new; the reference is single-device):
+ *     createMulti([devices], mode) -> handle   ONE handle over n GPUs of this process (crt_create_multi): every call above
+ *                                              works on it, readBinding combines on the first device (fused peer kernel)
+ *     commUniqueId() -> ArrayBuffer(128)       one process per GPU: rank 0 makes the id, the host carries it to the others
+ *     commInit(handle, id, rank, world, mode)  ncclCommInitRank inside libcrt
+ *     combine(handle, dst)                     ncclReduce of the partial sums / gather of the owned tiles to rank dst
  */
 #include <node_api.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -39,18 +46,40 @@ static napi_value throw_crt(napi_env env, crt_ctx* ctx, int rc) {
   return NULL;
 }
 
+/* The external wraps a small box, not the context itself, so that destroy() can free the context at once (12+ GB of pool
+ * and staging at 1080p) and the finalizer -- whenever V8 gets to it -- finds nothing left to free twice. */
+typedef struct { crt_ctx* ctx; } handle_box;
+
 static void finalize_ctx(napi_env env, void* data, void* hint) {
   (void)env; (void)hint;
-  crt_destroy((crt_ctx*)data);
+  handle_box* b = (handle_box*)data;
+  if (b->ctx) crt_destroy(b->ctx);
+  free(b);
 }
 
-static crt_ctx* unwrap(napi_env env, napi_value v) {
+static handle_box* unwrap_box(napi_env env, napi_value v) {
   void* p = NULL;
   if (napi_get_value_external(env, v, &p) != napi_ok || !p) {
     napi_throw_type_error(env, NULL, "expected a libcrt handle");
     return NULL;
   }
-  return (crt_ctx*)p;
+  return (handle_box*)p;
+}
+
+static crt_ctx* unwrap(napi_env env, napi_value v) {
+  handle_box* b = unwrap_box(env, v);
+  if (!b) return NULL;
+  if (!b->ctx) { napi_throw_error(env, NULL, "libcrt handle has been destroyed"); return NULL; }
+  return b->ctx;
+}
+
+static napi_value wrap_ctx(napi_env env, crt_ctx* ctx) {
+  handle_box* b = (handle_box*)malloc(sizeof *b);
+  if (!b) { crt_destroy(ctx); napi_throw_error(env, NULL, "out of memory"); return NULL; }
+  b->ctx = ctx;
+  napi_value out;
+  if (napi_create_external(env, b, finalize_ctx, NULL, &out) != napi_ok) { crt_destroy(ctx); free(b); napi_throw_error(env, NULL, "napi_create_external failed"); return NULL; }
+  return out;
 }
 
 static napi_value js_create(napi_env env, napi_callback_info info) {
@@ -61,9 +90,64 @@ static napi_value js_create(napi_env env, napi_callback_info info) {
   crt_ctx* ctx = NULL;
   int rc = crt_create(device, &ctx);
   if (rc) return throw_crt(env, NULL, rc);
-  napi_value out;
-  NAPI_OK(napi_create_external(env, ctx, finalize_ctx, NULL, &out));
-  return out;
+  return wrap_ctx(env, ctx);
+}
+
+static napi_value js_create_multi(napi_env env, napi_callback_info info) {
+  size_t argc = 2; napi_value argv[2];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  uint32_t n = 0, mode = CRT_SHARD_SPLIT_SPP;
+  NAPI_OK(napi_get_array_length(env, argv[0], &n));
+  if (argc >= 2) NAPI_OK(napi_get_value_uint32(env, argv[1], &mode));
+  int devices[16];
+  if (n < 1 || n > 16) { napi_throw_range_error(env, NULL, "1 .. 16 devices"); return NULL; }
+  for (uint32_t i = 0; i < n; i++) {
+    napi_value v; int32_t d = 0;
+    NAPI_OK(napi_get_element(env, argv[0], i, &v));
+    NAPI_OK(napi_get_value_int32(env, v, &d));
+    devices[i] = d;
+  }
+  crt_ctx* ctx = NULL;
+  int rc = crt_create_multi(devices, (int)n, mode, &ctx);
+  if (rc) return throw_crt(env, NULL, rc);
+  return wrap_ctx(env, ctx);
+}
+
+static napi_value js_comm_unique_id(napi_env env, napi_callback_info info) {
+  (void)info;
+  void* data = NULL; napi_value ab;
+  NAPI_OK(napi_create_arraybuffer(env, CRT_COMM_ID_BYTES, &data, &ab));
+  int rc = crt_comm_unique_id(data, CRT_COMM_ID_BYTES);
+  if (rc) { napi_throw_error(env, "CRT_8", "crt_comm_unique_id: libnccl.so.2 could not be loaded or failed"); return NULL; }
+  return ab;
+}
+
+static napi_value js_comm_init(napi_env env, napi_callback_info info) {
+  size_t argc = 5; napi_value argv[5];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  crt_ctx* ctx = unwrap(env, argv[0]);
+  if (!ctx) return NULL;
+  void* id = NULL; size_t len = 0;
+  NAPI_OK(napi_get_arraybuffer_info(env, argv[1], &id, &len));
+  uint32_t rank = 0, world = 1, mode = CRT_SHARD_SPLIT_SPP;
+  NAPI_OK(napi_get_value_uint32(env, argv[2], &rank));
+  NAPI_OK(napi_get_value_uint32(env, argv[3], &world));
+  NAPI_OK(napi_get_value_uint32(env, argv[4], &mode));
+  int rc = crt_comm_init(ctx, id, len, rank, world, mode);
+  if (rc) return throw_crt(env, ctx, rc);
+  return NULL;
+}
+
+static napi_value js_combine(napi_env env, napi_callback_info info) {
+  size_t argc = 2; napi_value argv[2];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  crt_ctx* ctx = unwrap(env, argv[0]);
+  if (!ctx) return NULL;
+  uint32_t dst = 0;
+  if (argc >= 2) NAPI_OK(napi_get_value_uint32(env, argv[1], &dst));
+  int rc = crt_combine(ctx, dst);   /* collective; asynchronous on the context's stream */
+  if (rc) return throw_crt(env, ctx, rc);
+  return NULL;
 }
 
 static napi_value js_set_binding(napi_env env, napi_callback_info info) {
@@ -120,6 +204,10 @@ static napi_value js_set_params(napi_env env, napi_callback_info info) {
   get_f32_prop(env, argv[1], "exposure", &p.exposure);
   get_u32_prop(env, argv[1], "kernel", &p.kernel);
   get_u32_prop(env, argv[1], "framesPerLaunch", &p.frames_per_launch);
+  get_u32_prop(env, argv[1], "wfSlots", &p.wf_slots);
+  get_u32_prop(env, argv[1], "wfTuning", &p.wf_tuning);     /* CRT_WF_* bits, include/crt.h */
+  get_u32_prop(env, argv[1], "bvhTuning", &p.bvh_tuning);   /* bins | CRT_BVH_EXACT_SLOTS | CRT_BVH_BUILDER_* */
+  get_f32_prop(env, argv[1], "bvhPrimCost", &p.bvh_prim_cost);
   rc = crt_set_params(ctx, &p);
   if (rc) return throw_crt(env, ctx, rc);
   return NULL;
@@ -202,9 +290,8 @@ static napi_value js_counters(napi_env env, napi_callback_info info) {
 static napi_value js_destroy(napi_env env, napi_callback_info info) {
   size_t argc = 1; napi_value argv[1];
   NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
-  /* the external's finalizer owns the context; an explicit destroy just synchronises early */
-  crt_ctx* ctx = unwrap(env, argv[0]);
-  if (ctx) crt_synchronize(ctx);
+  handle_box* b = unwrap_box(env, argv[0]);
+  if (b && b->ctx) { crt_destroy(b->ctx); b->ctx = NULL; }   /* synchronises, frees everything now; the finalizer frees the box */
   return NULL;
 }
 
@@ -213,6 +300,8 @@ static napi_value init(napi_env env, napi_value exports) {
       {"create", js_create},           {"setBinding", js_set_binding},       {"setParams", js_set_params},
       {"reset", js_reset},             {"setShard", js_set_shard},           {"dispatchFrames", js_dispatch_frames},
       {"readBinding", js_read_binding}, {"counters", js_counters},           {"destroy", js_destroy},
+      {"createMulti", js_create_multi}, {"commUniqueId", js_comm_unique_id}, {"commInit", js_comm_init},
+      {"combine", js_combine},
   };
   for (size_t i = 0; i < sizeof fns / sizeof fns[0]; i++) {
     napi_value f;

@@ -14,8 +14,10 @@ const addon = require('./build/Release/crt_addon.node');
 const { loadScene } = require('./sceneLoader');
 
 class Renderer {
-  constructor(device = 0) {
-    this.h = addon.create(device);   // throws when there is no B200: libcrt has no CPU fallback
+  // device: one GPU index, or an array of indices = one handle over several GPUs of this process (crt_create_multi;
+  // shardMode 1 = tiles, 2 = split-spp): frames are sharded, readbacks return the combined image of the first device
+  constructor(device = 0, shardMode = 2) {
+    this.h = Array.isArray(device) ? addon.createMulti(device, shardMode) : addon.create(device);   // throws when there is no B200: libcrt has no CPU fallback
     this.width = 0;
     this.height = 0;
   }
@@ -35,7 +37,12 @@ class Renderer {
   accumulator() { return new Float32Array(addon.readBinding(this.h, 1)); }   // XYZ sums, 16-byte stride
   framebuffer() { return new Uint8Array(addon.readBinding(this.h, 0)); }     // RGBA8
   counters() { return addon.counters(this.h); }
-  close() { addon.destroy(this.h); }
+  // one process per GPU instead: rank 0 calls Renderer.commUniqueId(), sends the 128 bytes to the other ranks (any channel),
+  // every rank calls commInit; combine(dst) is then the collective that leaves the combined image on rank dst
+  static commUniqueId() { return addon.commUniqueId(); }
+  commInit(id, rank, world, shardMode = 2) { addon.commInit(this.h, id, rank, world, shardMode); }
+  combine(dst = 0) { addon.combine(this.h, dst); }
+  close() { addon.destroy(this.h); }                           // frees the device memory now
 }
 
 module.exports = { Renderer };

@@ -365,31 +365,34 @@ def test_soup_200k_radiance_parity_vs_oracle_bvh(gpu, oracle):
     assert cg == (int(cc[0]), int(cc[1]), int(cc[2]))
 
 
+@pytest.mark.parametrize("tail", [0, 31 << 8], ids=["tail_default", "tail_off"])
 @pytest.mark.parametrize("wf_slots,chunk", [(1024, 0), (4096, 2), (0, 3), (100_000, 7)])
-def test_wavefront_pool_and_chunk_size_never_change_results(gpu, oracle, wf_slots, chunk):
+def test_wavefront_pool_and_chunk_size_never_change_results(gpu, oracle, wf_slots, chunk, tail):
     """The path-slot pool (how many paths are in flight, which slot runs which pixel-sample) and the chunk length (how
     many frames share a wavefront) are scheduling only: accumulator, framebuffer and counters stay those of the oracle."""
     ps = scenes.mesh_scene(96, 64, n_lon=64, n_lat=32)
     gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
-    acc, fb, cg = _render(gpu, 7, kernel=2, max_depth=8, wf_slots=wf_slots, frames_per_launch=chunk)
+    acc, fb, cg = _render(gpu, 7, kernel=2, max_depth=8, wf_slots=wf_slots, frames_per_launch=chunk, wf_tuning=tail)
     acc_c, fb_c, cc = oracle.scene(ps, default_params(max_depth=8)).render(7)
     assert_radiance(acc, acc_c, 7)
     assert np.array_equal(fb, fb_c)
     assert cg == (int(cc[0]), int(cc[1]), int(cc[2]))
 
 
+@pytest.mark.parametrize("tail", [0, 31 << 8, 5 << 8, 13 << 8], ids=["tail_default", "tail_off", "tail_16", "tail_4096"])
 @pytest.mark.parametrize("host_loop", [0, 16], ids=["graph_loop", "host_loop"])
 @pytest.mark.parametrize("live,defer", [(1, 4), (2, 4), (3, 4), (3, 8), (2, 8)])
 @pytest.mark.parametrize("maker,kw", [(scenes.mesh_scene, dict(n_lon=64, n_lat=32)), (scenes.default_scene, {})])
-def test_wavefront_scheduling_forms_never_change_results(gpu, oracle, maker, kw, live, defer, host_loop):
+def test_wavefront_scheduling_forms_never_change_results(gpu, oracle, maker, kw, live, defer, host_loop, tail):
     """How wf_logic's live slots reach the next iteration (crt_params.wf_tuning: 1 one live list; 2 finish and bounce lists
     filled by wf_logic and wf_traverse; 3 class bytes + wf_partition -- in 2 and 3 a warp's lanes are in one phase, and with
     CRT_WF_DEFER_ON a path that ends in a bounce warp is finished by the next iteration's finish warps) and who runs the
-    iteration loop (the CUDA-graph WHILE node on the device, or the host) decide which thread runs which pixel-sample
-    when, nothing else: accumulator, framebuffer and counters stay the oracle's.  A small pool forces many rounds per slot."""
+    iteration loop (the CUDA-graph WHILE node on the device, or the host) and when it hands the last live slots to wf_tail
+    (never, at 16 / 4096 / the default 32768 slots) decide which thread runs which pixel-sample when, nothing else:
+    accumulator, framebuffer and counters stay the oracle's.  A small pool forces many rounds per slot."""
     ps = maker(96, 64, **kw)
     gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
-    acc, fb, cg = _render(gpu, 7, kernel=2, max_depth=8, wf_slots=2048, frames_per_launch=0, wf_tuning=live | defer | host_loop)
+    acc, fb, cg = _render(gpu, 7, kernel=2, max_depth=8, wf_slots=2048, frames_per_launch=0, wf_tuning=live | defer | host_loop | tail)
     acc_c, fb_c, cc = oracle.scene(ps, default_params(max_depth=8)).render(7)
     assert_radiance(acc, acc_c, 7)
     assert np.array_equal(fb, fb_c)
@@ -557,7 +560,10 @@ def test_adversarial_rays_bit_exact_vs_linear_scan(gpu, oracle):
         for ex in (None, rng.integers(0, min(n_prims, 12), size=rays.shape[0]).astype(np.uint32)):
             gi, gt = gpu.trace_rays(rays, ex)
             ci, ct, _ = sc.trace_rays(rays, ex)
-            bad = np.nonzero((gi != ci) | (gt.view(np.uint32) != ct.view(np.uint32)))[0]
+            # (a NaN ray is accepted by the written sense of CS:557 and carries t = NaN; NaN payloads differ between x86 and
+            # the GPU, every consumer only tests "is NaN": NaN == NaN here, everything else bit for bit)
+            same_t = (gt.view(np.uint32) == ct.view(np.uint32)) | (np.isnan(gt) & np.isnan(ct))
+            bad = np.nonzero((gi != ci) | ~same_t)[0]
             assert bad.size == 0, (bad[:5], rays[bad[:5]], gi[bad[:5]], ci[bad[:5]], gt[bad[:5]], ct[bad[:5]])
         assert len(np.unique(ci)) >= 8
     # the same rays as a render cannot be issued, but NaN-producing paths can: a 2-frame render of the triangle scene stays bit-exact
@@ -730,9 +736,16 @@ def test_full_size_config5_soup10m_tile_sample(gpu, oracle):
     assert cg[0] == 1920 * 1080 * 2 and np.isfinite(acc[..., :3]).all()
     sc = oracle.scene(ps, default_params(max_depth=8), use_bvh=True)
     cpu, _, cc = sc.render(2, rank=5, world=128, mode=SHARD_TILES, want_fb=False)
-    own = cpu[..., :3].any(axis=-1)
-    assert own.sum() > 8000
+    # (ten million triangles fill the box: the light is occluded almost everywhere and most pixels are exactly black, so the
+    # shard's pixels are taken from the tile ownership, not from "non-zero")
+    from computeraytracer_b200 import multi
+    units = multi.tile_units(1920, 1080, 5, 128)
+    own = np.zeros(1920 * 1080, dtype=bool); own[units[units >= 0]] = True
+    own = own.reshape(1080, 1920)
+    assert own.sum() > 16000 and int(cc[0]) == 2 * int(own.sum()) and int(cc[1]) > 3 * int(own.sum())
+    assert not cpu[~own][:, :3].any()
     assert np.array_equal(acc[own][:, :3].view(np.uint32), cpu[own][:, :3].view(np.uint32))
+    assert acc[..., :3].any()
     rays = scenes.camera_rays(ps, 20000, seed=3)
     gi, gt = gpu.trace_rays(rays)
     ci, ct, _ = sc.trace_rays(rays)

@@ -144,3 +144,37 @@ def test_primary_hit_histogram(oracle, size, want):
     moved = sum(abs(got[k] - want[k]) for k in want)
     assert moved <= 12, (moved, {k: (got[k], want[k]) for k in want if got[k] != want[k]})
     assert sum(got.values()) == size * size
+
+
+def test_detmath_is_accurate_against_double_libm(oracle):
+    """include/crt_detmath.h is compiled into the oracle AND the kernels, so GPU == oracle says nothing about its accuracy
+    (VERDICT r1, weak-1).  Against numpy's double-precision libm: sin and cos within 2 ulp on [0, 2 pi] (the only range
+    the shader feeds them, CS:754-758: theta = 2 pi v, v in [0, 1)), exp within 2 ulp on [-87, 10] (CS:177, 438: arguments are
+    -extinction x distance and -colour x exposure, never positive beyond the tone map's clamp; results below FLT_MIN flush
+    towards zero), pow(x, 1/2.4) within 3e-7 relative on [0.0031308, 1] (the sRGB curve's domain, CS:449-465)."""
+    rng = np.random.default_rng(42)
+
+    def ulps(got, want64):
+        want32 = want64.astype(np.float32)
+        return np.abs(got.astype(np.float64) - want64) / np.spacing(np.abs(want32)).astype(np.float64)
+
+    x = np.concatenate([rng.uniform(0.0, 2 * np.pi, 400_000), np.linspace(0, 2 * np.pi, 4097), [0.0, np.pi / 2, np.pi, 1.5 * np.pi]]).astype(np.float32)
+    s, c, _, _ = oracle.detmath(x)
+    x64 = x.astype(np.float64)
+    # near the zeros of sin / cos an ulp of the RESULT is tiny while the argument itself carries half an ulp of 2 pi: bound
+    # the absolute error there (2^-24) and the ulp error elsewhere
+    for got, want in ((s, np.sin(x64)), (c, np.cos(x64))):
+        big = np.abs(want) > 1e-2
+        assert ulps(got[big], want[big]).max() <= 2.0
+        assert np.abs(got[~big].astype(np.float64) - want[~big]).max() <= 2.0 ** -24
+    xe = np.concatenate([rng.uniform(-87.0, 10.0, 400_000), np.linspace(-87, 10, 4097), [0.0, -0.0, 1.0, -1.0]]).astype(np.float32)
+    _, _, e, _ = oracle.detmath(xe)
+    assert ulps(e, np.exp(xe.astype(np.float64))).max() <= 2.0
+    _, _, e, _ = oracle.detmath(np.array([-104.0, -200.0, -1e30, -np.inf], dtype=np.float32))
+    assert np.all(e >= 0.0) and np.all(e < 1e-44)                       # far underflow: zero (or the smallest denormals), never garbage
+    _, _, e, _ = oracle.detmath(np.array([np.nan], dtype=np.float32))
+    assert np.isnan(e[0])
+    xp = np.concatenate([rng.uniform(0.0031308, 1.0, 400_000), np.linspace(0.0031308, 1.0, 4097)]).astype(np.float32)
+    _, _, _, p = oracle.detmath(xp)
+    want = xp.astype(np.float64) ** (1.0 / 2.4)
+    assert (np.abs(p.astype(np.float64) - want) / want).max() <= 3e-7
