@@ -68,6 +68,7 @@ def parse_args():
     ap.add_argument("--wf-tuning", type=lambda s: int(s, 0), default=0, help="crt_params.wf_tuning bits (include/crt.h)")
     ap.add_argument("--bvh-tuning", type=lambda s: int(s, 0), default=0, help="crt_params.bvh_tuning bits: bins | 0x200 exact slots")
     ap.add_argument("--bvh-prim-cost", type=float, default=0.0)
+    ap.add_argument("--max-depth", type=int, default=-1, help="override the workload's max_depth (experiments: 0 = primary rays only)")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the secondary measurements (Cornell config 2, single-frame dispatches, FP32 peak)")
@@ -250,6 +251,8 @@ def run_b200(args):
     dev = f"cuda:{device}"
 
     ps, max_depth, desc = workload_scene(args.workload, args.width, args.height)
+    if args.max_depth >= 0:
+        max_depth = args.max_depth
     r = Renderer(device)
     r.set_stream(stream.cuda_stream)
     bvh_bits = args.bvh_tuning | {"auto": 0, "host": BVH_BUILDER_HOST_SAH, "device": BVH_BUILDER_DEVICE}[args.bvh]

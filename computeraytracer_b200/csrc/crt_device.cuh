@@ -171,7 +171,9 @@ struct Hit {
 // patch test (CS:563-566) uses u and v for nothing but this comparison; two of its three divisions go away for every
 // ray that reaches it (ncu r01: IEEE divisions are 12 % of wf_logic's instructions).
 __device__ __forceinline__ bool outside_unit(float a, float b) {
+#ifndef CRT_UV_DIVIDE   // (A/B switch: the plain divisions)
   if (b > 0.0f && b < 1e18f && !(a < 0.0f && a > -1e-18f)) return a < 0.0f || a > b;
+#endif
   const float q = a / b;
   return q < 0.0f || q > 1.0f;
 }

@@ -509,7 +509,11 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
   const float *spectra, *cie;
   wf_tables(sc, w, s_tables, spectra, cie);
   const WfChunk& ck = s_ck;
+#ifdef WF_IT_PARAM   // (A/B switch, host loop only: the iteration number straight from the kernel parameter)
+  const uint32_t it = it_arg;
+#else
   const uint32_t it = s_it;
+#endif
   // Routed forms (`routed` = WF_LIVE_ROUTED or WF_LIVE_CLASS): the live slots arrive in two lists -- the finish list (extension ray missed, or only an NEE
   // answer was outstanding: these lanes finish the path and start the next one) padded to whole warps, then the bounce
   // list (surface hit: these lanes shade) -- so the lanes of a warp are in the same phase of this kernel.  wf_emit and

@@ -108,7 +108,7 @@ typedef struct crt_params {
 #define CRT_WF_TAIL_SHIFT 8
 #define CRT_WF_TAIL_MASK (31u << CRT_WF_TAIL_SHIFT)
 #define CRT_WF_TAIL_OFF (31u << CRT_WF_TAIL_SHIFT)
-#define CRT_WF_TAIL_DEFAULT 32768u
+#define CRT_WF_TAIL_DEFAULT 131072u
 /* bvh_tuning */
 #define CRT_BVH_BINS_MASK 0x1FFu
 #define CRT_BVH_EXACT_SLOTS 0x200u

@@ -388,7 +388,7 @@ def test_wavefront_scheduling_forms_never_change_results(gpu, oracle, maker, kw,
     filled by wf_logic and wf_traverse; 3 class bytes + wf_partition -- in 2 and 3 a warp's lanes are in one phase, and with
     CRT_WF_DEFER_ON a path that ends in a bounce warp is finished by the next iteration's finish warps) and who runs the
     iteration loop (the CUDA-graph WHILE node on the device, or the host) and when it hands the last live slots to wf_tail
-    (never, at 16 / 4096 / the default 32768 slots) decide which thread runs which pixel-sample when, nothing else:
+    (never, at 16 / 4096 / the default 131072 slots) decide which thread runs which pixel-sample when, nothing else:
     accumulator, framebuffer and counters stay the oracle's.  A small pool forces many rounds per slot."""
     ps = maker(96, 64, **kw)
     gpu.set_scene(ps); gpu.set_shard(0, 1, 0)

@@ -11,7 +11,7 @@ import sys, json
 l = sys.stdin.read().strip()
 try:
     d = json.loads(l); k = d['roofline']['kernels_ms_per_step']
-    print(round(d['value']), 'Mrays/s', round(d['ms_per_step'], 1), 'ms', {a: round(b, 1) for a, b in k.items()}, 'launches', d['gpu_launches'], 'paths', int(d['rays']['paths']), 'ext', int(d['rays']['ext']))
+    print(round(d['value']), 'Mrays/s', round(d['ms_per_step'], 1), 'ms', {a: round(b, 1) for a, b in k.items()}, 'launches', d['gpu_launches'], 'paths', int(d['rays']['paths']), 'ext', int(d['rays']['ext']), 'shadow', int(d['rays']['shadow']), 'nodes/ray', round(d['roofline']['nodes_per_ray'], 2), 'tris/ray', round(d['roofline']['tris_per_ray'], 2), 'queued/ray', round(d['roofline']['bvh_rays_per_ray'], 3), 'bvh_ms', round(d['bvh_build_ms'], 1))
 except Exception as e:
     print('FAILED', l[-300:])
 ")
