@@ -16,6 +16,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <unordered_map>
 #include <unordered_set>
 #include <utility>
 #include <vector>
@@ -65,7 +66,7 @@ struct crt_ctx {
   float* d_cam = nullptr;        // 64 bytes of binding 4 + 48 bytes of camera constants
   size_t acc_pixels = 0;
   float* d_spectra = nullptr; float* d_cie = nullptr;
-  LinPrim* d_lin = nullptr; LightRec* d_lights = nullptr;
+  LinPrim* d_lin = nullptr; LightRec* d_lights = nullptr; uint32_t* d_light_mask = nullptr;
   float4* d_tri = nullptr; uint4* d_nodes = nullptr;   // one allocation: nodes, then triangles (d_tri points into it)
   size_t scene_bytes = 0;
   uint32_t* d_work = nullptr;
@@ -386,14 +387,24 @@ int upload_scene(crt_ctx* ctx) {
   CU(cudaStreamSynchronize(ctx->stream));
   s.lights_g = ctx->d_lights;
 
-  // does any light's primitive (data4.w, CS:386) live in the BVH?  then shadow rays need closest-hit
-  s.shadow_closest = 0;
+  // does any light's primitive (data4.w, CS:386) live in the BVH?  then shadow rays towards it need closest-hit
+  s.shadow_closest = 0; s.light_tri_mask = nullptr;
+  dfree(ctx->d_light_mask);
   if (!tri_pos.empty()) {
-    std::unordered_set<uint32_t> light_prims;
-    for (size_t l = 0; l < n_lights; l++) { uint32_t want; memcpy(&want, ctx->b_lights.data() + l * 80 + 76, 4); light_prims.insert(want); }
+    std::unordered_map<uint32_t, std::vector<uint32_t>> light_prims;   // primitive index -> the lights that name it
+    for (size_t l = 0; l < n_lights; l++) { uint32_t want; memcpy(&want, ctx->b_lights.data() + l * 80 + 76, 4); light_prims[want].push_back((uint32_t)l); }
+    std::vector<uint32_t> mask((n_lights + 31) / 32, 0u);
     for (uint32_t p : tri_pos) {
       uint32_t idx; memcpy(&idx, prims + (size_t)p * 80 + 76, 4);
-      if (light_prims.count(idx)) { s.shadow_closest = 1; break; }
+      auto it = light_prims.find(idx);
+      if (it == light_prims.end()) continue;
+      s.shadow_closest = 1;
+      for (uint32_t l : it->second) mask[l >> 5] |= 1u << (l & 31u);
+    }
+    if (s.shadow_closest) {
+      CU(cudaMalloc(&ctx->d_light_mask, mask.size() * 4));
+      CU(cudaMemcpy(ctx->d_light_mask, mask.data(), mask.size() * 4, cudaMemcpyHostToDevice));
+      s.light_tri_mask = ctx->d_light_mask;
     }
   }
   const auto t1 = std::chrono::steady_clock::now();
@@ -815,7 +826,7 @@ void crt_destroy(crt_ctx* ctx) {
   if (ctx->nccl_comm) { if (NcclApi* nc = nccl_api()) nc->CommDestroy(ctx->nccl_comm); ctx->nccl_comm = nullptr; }
   drop_wf_graph(ctx);
   dfree(ctx->d_acc); dfree(ctx->d_fb); dfree(ctx->d_tea); dfree(ctx->d_cam); dfree(ctx->d_spectra); dfree(ctx->d_cie);
-  dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_nodes); dfree(ctx->d_work); dfree(ctx->d_counters);
+  dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_light_mask); dfree(ctx->d_nodes); dfree(ctx->d_work); dfree(ctx->d_counters);
   dfree(ctx->d_comb); dfree(ctx->d_xfer);
   if (ctx->wf_mem) cudaFree(ctx->wf_mem);
   if (ctx->wf_stage) cudaFree(ctx->wf_stage);
@@ -995,13 +1006,8 @@ int crt_dispatch_frames(crt_ctx* ctx, uint32_t n) {
   uint32_t kernel = ctx->params.kernel;
   if (kernel == CRT_KERNEL_AUTO)
     kernel = (ctx->params.max_depth <= 1000 && (s.n_tri > 0 || n >= 2)) ? CRT_KERNEL_WAVEFRONT : CRT_KERNEL_MEGA;
-  // a light that is itself a triangle needs closest-hit shadow rays: only the megakernel carries that path (AUTO goes
-  // there; asking for the wavefront form by name is refused rather than silently overridden)
-  if (s.shadow_closest) {
-    if (ctx->params.kernel == CRT_KERNEL_WAVEFRONT)
-      return fail(ctx, CRT_ERR_STATE, "a light of this scene is a triangle: its shadow rays need closest-hit traversal, which only CRT_KERNEL_MEGA has (use AUTO)");
-    kernel = CRT_KERNEL_MEGA;
-  }
+  // (a light that is itself a triangle needs closest-hit shadow rays: both forms carry that path -- crt_device.cuh
+  // shadow_intersect, crt_wavefront.cu NeeQuery::tri)
   CU(cudaEventRecord(ctx->ev_start, ctx->stream));
   if (kernel == CRT_KERNEL_WAVEFRONT) {
     if (n) { rc = dispatch_wavefront(ctx, n, n_units, stats); if (rc) return rc; }

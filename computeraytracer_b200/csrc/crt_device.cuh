@@ -67,7 +67,8 @@ struct DevScene {
   uint32_t n_tri, n_nodes;
   const float4* tri;              // 3 x float4 per triangle, BVH leaf order
   const uint4* nodes;             // 5 x 16 bytes per 8-wide node ("Wide8" below)
-  uint32_t shadow_closest;        // 1: some light's primitive is a triangle -> shadow rays need closest-hit
+  uint32_t shadow_closest;        // 1: some light's primitive is a triangle -> shadow rays towards it need closest-hit
+  const uint32_t* light_tri_mask; // shadow_closest scenes: bit li set = light li's primitive (data4.w) is a triangle
   float bvh_lo[3], bvh_hi[3];     // padded bounds of all triangles (root box)
   // sharding
   uint32_t rank, world, shard_mode;

@@ -42,8 +42,10 @@ enum {
   WF_R_H = 2, WF_R_S5 = 3,    // sector B: hit of the extension ray; exclude, depth|flags|wavelength, sampled light's primitive, work item
   WF_R_S6 = 4, WF_R_S7 = 5,   // sector C: pending NEE shadow ray (direction, light distance) and contribution
   WF_R_S3 = 6, WF_R_S4 = 7,   // sector D: beta, RNG state
-  WF_R_S2 = 8                 // sector E: accumulated radiance L (+ 16 bytes spare) -- on its own, because a pass touches it
+  WF_R_S2 = 8,                // sector E: accumulated radiance L -- on its own, because a pass touches it
                               // only when it adds to L or finishes the path (WF_FLAG_LZERO: never written yet, reads as 0)
+  WF_R_S8 = 9                 // sector E, second word: only in scenes where a light is a triangle (sc.shadow_closest) -- what the
+                              // deferred NEE contribution towards such a light is rebuilt from (NeeQuery::aux)
 };
 // Record accessors.  (Measured and rejected: sending the record stream through L2 with an evict-first policy -- wf_traverse
 // and the next wf_logic find the records in L2 today, profiles/r01t_static_l2_tri2_variants.txt.)
@@ -117,13 +119,45 @@ __device__ __forceinline__ void wf_push(bool pred, uint32_t entry, uint32_t* __r
 
 // The shadow ray of next-event estimation that still needs the BVH: the light is the closest hit of the linear list at
 // distance t, the contribution c = (BRDF * Le * w / pdf_l) * beta is final unless a triangle occludes the segment.
+// When the sampled light's primitive is itself a triangle, the linear list cannot have found it: the query is a CLOSEST-hit
+// traversal that starts from the linear list's hit (t < 0 in the record marks it: bound -t), and the contribution can only be
+// computed once the hit on the light is known (CS:393 needs its normal and position).  Then c carries beta as it was at the
+// bounce and aux = (cos_theta, reflectance index | light << 12, -, index of the linear list's hit); wf_tri_contribution
+// rebuilds BRDF, Le, the MIS weight and the product in the reference's order when the answer is there.
 struct NeeQuery {
   bool pending;
+  bool tri;
   V3 d;
   float t;
   uint32_t light_prim;
   float4 c;
+  float4 aux;
 };
+
+// CS:388-400 + CS:187 for a shadow ray whose closest hit turned out to be the sampled triangle light: origin o, direction d,
+// hit (t, light_prim, ref) from the traversal; beta / cos_theta / reflectance / light as saved at the bounce.
+__device__ __forceinline__ float4 wf_tri_contribution(const DevScene& sc, const float* __restrict__ spectra, V3 o, V3 d, float t, uint32_t light_prim,
+                                                      uint32_t ref, float4 beta, float4 aux, uint32_t lam0, bool visible) {
+  uint32_t lam[4];
+  wavelengths(lam0, lam);
+  const float cos_theta = aux.x;
+  const uint32_t packed = __float_as_uint(aux.y);
+  const float4 refl = sample_spectrum(spectra, sc.n_spectra, packed & 0xFFFu, lam);
+  const float4 BRDF = make_float4(refl.x / CRT_PI_F, refl.y / CRT_PI_F, refl.z / CRT_PI_F, refl.w / CRT_PI_F);  // CS:184
+  float4 le = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                                                             // CS:407
+  if (visible) {
+    const LightRec& light = light_at(sc, (packed >> 12) & 0xFFFu);
+    const float4 spec = sample_spectrum(spectra, sc.n_spectra, __float_as_uint(light.d2.w), lam);
+    le = make_float4(spec.x * cos_theta, spec.y * cos_theta, spec.z * cos_theta, spec.w * cos_theta);
+    Hit hs; hs.t = t; hs.idx = light_prim; hs.ref = ref;
+    const Surface sh = surface_of(sc, hs, o, d);
+    const float pdf_l = compute_light_pdf(sc, CRT_META_EMIS(sh.meta), sh.normal, sh.position, o, d);            // CS:393
+    const float pdf_b = crt_div(cos_theta, CRT_PI_F);
+    const float w = power_heuristic(pdf_l, pdf_b);
+    le = make_float4(crt_div(le.x * w, pdf_l), crt_div(le.y * w, pdf_l), crt_div(le.z * w, pdf_l), crt_div(le.w * w, pdf_l));  // CS:400
+  }
+  return make_float4((BRDF.x * le.x) * beta.x, (BRDF.y * le.y) * beta.y, (BRDF.z * le.z) * beta.z, (BRDF.w * le.w) * beta.w);    // CS:187
+}
 
 // One bounce of path_trace's loop body (CS:133-293), entered with the hit `h` of the current extension ray and left with
 // the next extension ray in ps.o / ps.d / ps.exclude.  Unlike path_consume (crt_path.cuh), next-event estimation is not a
@@ -135,12 +169,12 @@ struct NeeQuery {
 // before anything else is added to L, so the order of the float additions is the reference's.
 // Returns 0: the path ended; 1: it continues with an extension ray; 2: Russian roulette ended it while nee.pending
 // (the slot must live on until the contribution has been added).
-template <bool STATS>
+template <bool STATS, bool TRI>
 __device__ __forceinline__ int wf_bounce(const DevScene& sc, const float* __restrict__ spectra, PathState& ps, Rng& rng, const Hit& h,
                                          Stats& st, uint32_t* term, uint32_t& n_shadow, NeeQuery& nee) {
   uint32_t lam[4];
   wavelengths(ps.lam0, lam);
-  nee.pending = false;
+  nee.pending = false; nee.tri = false;
   if (h.idx == CRT_MAX_U32) { if (STATS) term[0] = TERM_MISS; return 0; }      // CS:141-144
   ps.exclude = h.idx;                                                         // CS:146
   const Surface s = surface_of(sc, h, ps.o, ps.d);
@@ -196,11 +230,18 @@ __device__ __forceinline__ int wf_bounce(const DevScene& sc, const float* __rest
       }
     } else {
       le = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                                // CS:407
+      if (TRI && sc.shadow_closest && ((sc.light_tri_mask[li >> 5] >> (li & 31u)) & 1u) && hits_root_box(sc, s.position, light_dir, hs.t)) {
+        // the sampled light is a triangle: only a closest-hit traversal (bounded by the linear list's hit) can find it
+        add_now = false;
+        nee.pending = true; nee.tri = true; nee.d = light_dir; nee.t = -hs.t; nee.light_prim = include;
+        nee.aux = make_float4(cos_theta, __uint_as_float((CRT_META_REFL(s.meta) & 0xFFFu) | ((li & 0xFFFu) << 12) | 0x80000000u), 0.0f,
+                              __uint_as_float(hs.idx));
+      }
     }
     const float4 c = make_float4((BRDF.x * le.x) * ps.beta.x, (BRDF.y * le.y) * ps.beta.y, (BRDF.z * le.z) * ps.beta.z,
                                  (BRDF.w * le.w) * ps.beta.w);                 // CS:187
     if (add_now) { ps.L.x += c.x; ps.L.y += c.y; ps.L.z += c.z; ps.L.w += c.w; }
-    else nee.c = c;
+    else nee.c = nee.tri ? ps.beta : c;   // (a triangle light's contribution is computed when its hit is known: beta as it is now)
     const float u = rnd(rng), v = rnd(rng);
     if (STATS) st.rand_calls += 5;
     float pdf;
@@ -259,14 +300,25 @@ __device__ __forceinline__ void wf_finish(const DevScene& /*sc*/, const WfChunk&
 }
 
 // the pending NEE contribution of a slot, as the reference would have added it (CS:187 with CS:400 or CS:407)
-__device__ __forceinline__ float4 wf_pending(const WfState& w, uint32_t slot) {
-  const bool occluded = rec_ptr(w, slot, WF_R_S6)->w < 0.0f;   // wf_traverse marks an occluded segment by a negative length
+template <bool TRI>
+__device__ __forceinline__ float4 wf_pending(const DevScene& sc, const float* __restrict__ spectra, const WfState& w, uint32_t slot) {
+  const float4 q = rec_ld(w, slot, WF_R_S6);
+  const bool occluded = q.w < 0.0f;   // wf_traverse marks an occluded segment by a negative length
   float4 c = rec_ld(w, slot, WF_R_S7);
+  if (TRI && sc.shadow_closest) {
+    const float4 aux = rec_ld(w, slot, WF_R_S8);
+    if (__float_as_uint(aux.y) & 0x80000000u) {   // the query went to a triangle light: c is beta, the contribution is built now
+      const float4 a = rec_ld(w, slot, WF_R_S0);
+      const uint4 m = rec_ldu(w, slot, WF_R_S5);
+      return wf_tri_contribution(sc, spectra, v3(a), v3(q), q.w, m.z, __float_as_uint(aux.z), c, aux, (m.y >> 20) & 0x7FFu, !occluded);
+    }
+  }
   if (occluded) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407: Le = 0, the sum still happens
   return c;
 }
-__device__ __forceinline__ void wf_add_pending(const WfState& w, uint32_t slot, float4& L) {
-  const float4 c = wf_pending(w, slot);
+template <bool TRI>
+__device__ __forceinline__ void wf_add_pending(const DevScene& sc, const float* __restrict__ spectra, const WfState& w, uint32_t slot, float4& L) {
+  const float4 c = wf_pending<TRI>(sc, spectra, w, slot);
   L.x += c.x; L.y += c.y; L.z += c.z; L.w += c.w;
 }
 
@@ -315,7 +367,7 @@ __device__ __forceinline__ void wf_counts_flush(const LogicCounts& lc, const Sta
 // no list at all: the slot's class byte is written (w.cls: 0 bounce, 1 finish, 2 retired; wf_traverse corrects it when a
 // triangle turns a miss into a hit) and wf_partition builds both lists in slot order after the traversal.
 enum { WF_LIVE_LIST = 0, WF_LIVE_ROUTED = 1, WF_LIVE_CLASS = 2, WF_LIVE_DEFER = 0x100 };
-template <bool STATS>
+template <bool STATS, bool TRI>
 __device__ __forceinline__ void wf_emit(const DevScene& sc, const WfState& w, uint32_t it, uint32_t mode, bool valid, bool alive, bool has_ext, uint32_t slot,
                                         const PathState& ps, const Rng& rng, uint32_t wid, uint32_t flags, const NeeQuery& nee,
                                         Stats& st, LogicCounts& lc) {
@@ -341,6 +393,7 @@ __device__ __forceinline__ void wf_emit(const DevScene& sc, const WfState& w, ui
     if (shadow) {
       rec_st(w, slot, WF_R_S6, make_float4(nee.d.x, nee.d.y, nee.d.z, nee.t));
       rec_st(w, slot, WF_R_S7, nee.c);
+      if (TRI && sc.shadow_closest) rec_st(w, slot, WF_R_S8, nee.tri ? nee.aux : make_float4(0.0f, 0.0f, 0.0f, 0.0f));
     }
   }
   const uint32_t nx = (it + 1u) & 1u;
@@ -399,16 +452,16 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
     uint32_t slot = 0, wid = 0, flags = 0;
     PathState ps;
     Rng rng;
-    NeeQuery nee; nee.pending = false; nee.light_prim = 0;
+    NeeQuery nee; nee.pending = false; nee.tri = false; nee.light_prim = 0;
     if (i < n_cur) {
       slot = cur[i];
       wf_load(w, slot, ps, rng, wid, flags);
       ps.L = wf_load_L(w, slot, flags);
-      if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // before anything else is added to L
+      if (flags & WF_FLAG_PENDING) wf_add_pending<true>(sc, spectra, w, slot, ps.L);   // before anything else is added to L
       const float4 hv = rec_ld(w, slot, WF_R_H);
       Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
       uint32_t term = 0;
-      const int r = wf_bounce<STATS>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
+      const int r = wf_bounce<STATS, true>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
       if (STATS && r != 1) { lc.term_cnt[term - TERM_MISS]++; lc.depth_sum += ps.depth; }
       flags = (nee.pending ? WF_FLAG_PENDING : 0u) | (r == 2 ? WF_FLAG_DEAD : 0u);
       alive = r != 0;
@@ -418,7 +471,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_SHADE_MIN_BLOCKS) wf_shade(const 
       else rec_st(w, slot, WF_R_S2, ps.L);   // (the new flags carry no WF_FLAG_LZERO)
     }
     const PushTicket tr = wf_reserve(ended, &w.iter[it].n_regen);   // in flight while wf_emit scans the linear list
-    wf_emit<STATS>(sc, w, it, live_mode, i < n_cur, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
+    wf_emit<STATS, true>(sc, w, it, live_mode, i < n_cur, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
     wf_commit(tr, ended, slot, w.regen);
   }
   wf_counts_flush<STATS>(lc, st, counters);
@@ -459,7 +512,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
         const uint4 m = rec_ldu(w, slot, WF_R_S5);
         const uint32_t flags = ((m.y >> 16) & 0xFu) | ((m.y >> 20) & WF_FLAG_LZERO);
         float4 L = wf_load_L(w, slot, flags);
-        if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, L);
+        if (flags & WF_FLAG_PENDING) wf_add_pending<true>(sc, spectra, w, slot, L);
         wf_finish(sc, ck, cie, L, (m.y >> 20) & 0x7FFu, m.w);
         if (STATS && !(flags & WF_FLAG_DEAD)) { lc.term_cnt[0]++; lc.depth_sum += m.y & 0xFFFFu; }
       } else {
@@ -468,7 +521,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
     }
     PathState ps;
     Rng rng;
-    NeeQuery nee; nee.pending = false; nee.light_prim = 0;
+    NeeQuery nee; nee.pending = false; nee.tri = false; nee.light_prim = 0;
     while (mask != 0u) {
       first = __shfl_sync(0xffffffffu, first, __ffs(mask) - 1);
       if (need) {
@@ -489,7 +542,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
       mask = __ballot_sync(0xffffffffu, need);   // lanes that drew a unit outside the image fetch again
       if (mask != 0u && lane == (uint32_t)__ffs(mask) - 1u) first = atomicAdd(w.work, (uint32_t)__popc(mask));
     }
-    wf_emit<STATS>(sc, w, it, live_mode, i < n_cur, alive, alive, slot, ps, rng, wid, WF_FLAG_LZERO, nee, st, lc);
+    wf_emit<STATS, true>(sc, w, it, live_mode, i < n_cur, alive, alive, slot, ps, rng, wid, WF_FLAG_LZERO, nee, st, lc);
   }
   wf_counts_flush<STATS>(lc, st, counters);
 }
@@ -498,7 +551,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
 // hit (wf_bounce), and if the path ended finish it and start the slot's next path right here.  Lanes of a warp are in
 // different phases (ncu: ~17 of 32 active), but these kernels wait on memory and on dependent arithmetic rather than on
 // issue slots, and the fused form makes one pass over a slot's record per bounce instead of up to two.
-template <bool STATS>
+template <bool STATS, bool TRI>   // TRI: the scene has a triangle light (sc.shadow_closest); every other scene runs the variant without that code
 __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(const __grid_constant__ DevScene sc, const WfState w, uint32_t it_arg,
                                                      uint32_t routed, unsigned long long* __restrict__ counters) {
   extern __shared__ float s_tables[];
@@ -538,7 +591,7 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
     uint32_t slot = 0, wid = 0, flags = 0;
     PathState ps;
     Rng rng;
-    NeeQuery nee; nee.pending = false; nee.light_prim = 0;
+    NeeQuery nee; nee.pending = false; nee.tri = false; nee.light_prim = 0;
     const bool valid = i < n_cur && (i >= n_fin_pad || i < n_fin);   // not a padding lane of the finish list
     if (valid) {
       need = true;
@@ -554,13 +607,13 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
         wf_load(w, slot, ps, rng, wid, flags);
         const bool had_pending = (flags & WF_FLAG_PENDING) != 0u;
         const uint32_t lzero = flags & WF_FLAG_LZERO;
-        if (had_pending) { ps.L = wf_load_L(w, slot, lzero); wf_add_pending(w, slot, ps.L); }
+        if (had_pending) { ps.L = wf_load_L(w, slot, lzero); wf_add_pending<TRI>(sc, spectra, w, slot, ps.L); }
         int r = 0;
         if (!(flags & WF_FLAG_DEAD)) {
           const float4 hv = rec_ld(w, slot, WF_R_H);
           Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
           uint32_t term = 0;
-          r = wf_bounce<STATS>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
+          r = wf_bounce<STATS, TRI>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
           if (STATS && r != 1) { lc.term_cnt[term - TERM_MISS]++; lc.depth_sum += ps.depth; }
           // routed forms with WF_LIVE_DEFER: a path that ends in a warp of the bounce list (light hit, depth limit, Russian
           // roulette) is not finished here by the few lanes it happens to -- the slot goes to the finish list as a dead
@@ -608,7 +661,7 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
         }
       }
     }
-    wf_emit<STATS>(sc, w, it, routed, valid, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
+    wf_emit<STATS, TRI>(sc, w, it, routed, valid, alive, has_ext, slot, ps, rng, wid, flags, nee, st, lc);
   }
   wf_counts_flush<STATS>(lc, st, counters);
 }
@@ -645,22 +698,28 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_tail(const __grid_constant__ DevS
     uint32_t wid, flags;
     wf_load(w, slot, ps, rng, wid, flags);
     ps.L = wf_load_L(w, slot, flags);
-    if (flags & WF_FLAG_PENDING) wf_add_pending(w, slot, ps.L);   // the outstanding NEE answer first (the reference's order)
+    if (flags & WF_FLAG_PENDING) wf_add_pending<true>(sc, spectra, w, slot, ps.L);   // the outstanding NEE answer first (the reference's order)
     if (!(flags & WF_FLAG_DEAD)) {
       const float4 hv = rec_ld(w, slot, WF_R_H);
       Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
       for (;;) {
-        NeeQuery nee; nee.pending = false; nee.light_prim = 0;
+        NeeQuery nee; nee.pending = false; nee.tri = false; nee.light_prim = 0;
         uint32_t term = 0;
-        const int r = wf_bounce<STATS>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
+        const int r = wf_bounce<STATS, true>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
         if (STATS && r != 1) { lc.term_cnt[term - TERM_MISS]++; lc.depth_sum += ps.depth; }
         if (nee.pending) {
           // what wf_traverse answers for the shadow queue: does a triangle occlude the segment to the light?  (origin = the new
           // ray's origin, exclude = the surface just hit)
-          Hit hs; hs.t = nee.t; hs.idx = nee.light_prim; hs.ref = 0;
-          traverse<true, STATS>(sc, ps.o, nee.d, ps.exclude, sc.t_min, hs, st);
           float4 c = nee.c;
-          if (hs.idx != nee.light_prim) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407, as wf_pending does
+          if (nee.tri) {   // the light is a triangle: closest hit from the linear list's hit on, then the contribution (wf_pending)
+            Hit hs; hs.t = -nee.t; hs.idx = __float_as_uint(nee.aux.w); hs.ref = 0;
+            traverse<false, STATS>(sc, ps.o, nee.d, ps.exclude, sc.t_min, hs, st);
+            c = wf_tri_contribution(sc, spectra, ps.o, nee.d, hs.t, nee.light_prim, hs.ref, nee.c, nee.aux, ps.lam0, hs.idx == nee.light_prim);
+          } else {
+            Hit hs; hs.t = nee.t; hs.idx = nee.light_prim; hs.ref = 0;
+            traverse<true, STATS>(sc, ps.o, nee.d, ps.exclude, sc.t_min, hs, st);
+            if (hs.idx != nee.light_prim) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407, as wf_pending does
+          }
           ps.L.x += c.x; ps.L.y += c.y; ps.L.z += c.z; ps.L.w += c.w;
           lc.n_bvh_rays++;
         }
@@ -767,7 +826,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
 #endif
   int sp = 0;
   uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);   // node group and triangle group of the lane's ray (crt_device.cuh)
-  bool have = false, exhausted = false, anyhit = false, lin_miss = false;
+  bool have = false, exhausted = false, anyhit = false, shadow = false, lin_miss = false;   // shadow: the entry is an NEE query; anyhit: its mode
   uint32_t slot = 0, exclude = CRT_MAX_U32, light_prim = 0;
   V3 d = v3(0.0f, 0.0f, 1.0f);
   WideRay r = wide_ray(v3(0.0f, 0.0f, 0.0f), d);
@@ -791,18 +850,26 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
         if (q >= n) {
           exhausted = true;
         } else {
-          anyhit = q >= n_ext;
-          slot = anyhit ? w.shadow_list[q - n_ext] : queue[q];
+          shadow = q >= n_ext;
+          anyhit = shadow;
+          slot = shadow ? w.shadow_list[q - n_ext] : queue[q];
           const float4 a = rec_ld(w, slot, WF_R_S0);
           const uint4 m = rec_ldu(w, slot, WF_R_S5);
           exclude = m.x;
-          if (anyhit) {
+          if (shadow) {
             // the NEE shadow ray: the light (linear list) is the closest hit so far at distance b.w; any triangle accepted
             // under the tie rule within that bound occludes it (crt_device.cuh shadow_intersect)
             const float4 b = rec_ld(w, slot, WF_R_S6);
             d = v3(b);
             light_prim = m.z;
             h.t = b.w; h.idx = light_prim; h.ref = 0;
+            if (b.w < 0.0f) {
+              // ... unless the light is itself a triangle (sc.shadow_closest scenes): then this is a closest-hit query that
+              // starts from the linear list's hit (distance -b.w, its index in the aux word) and is visible only if the
+              // traversal ends on the light
+              anyhit = false;
+              h.t = -b.w; h.idx = __float_as_uint(rec_ptr(w, slot, WF_R_S8)->w);
+            }
           } else {
             const float4 b = rec_ld(w, slot, WF_R_S1), hv = rec_ld(w, slot, WF_R_H);
             d = v3(b);
@@ -841,7 +908,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
     }
     // ---- finished rays: a shadow ray leaves its answer in S6.w; an extension ray leaves its final hit and its slot goes
     //      to the next iteration's shade queue (surface) or finish queue (miss)
-    const bool fin_ext = done && !anyhit;
+    const bool fin_ext = done && !shadow;
     if (STATS && done) {
       max_nodes = max(max_nodes, ray_nodes);
       if (w.slow_min && ray_nodes >= w.slow_min) {
@@ -854,8 +921,13 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_TRAV_MIN_BLOCKS) wf_traverse(cons
       }
     }
     if (done) {
-      if (anyhit) {
-        if (h.idx != light_prim) rec_ptr(w, slot, WF_R_S6)->w = -1.0f;   // occluded
+      if (shadow) {
+        if (anyhit) {
+          if (h.idx != light_prim) rec_ptr(w, slot, WF_R_S6)->w = -1.0f;   // occluded
+        } else if (h.idx == light_prim) {   // closest-hit query towards a triangle light: visible, leave the hit (else the length stays negative)
+          rec_ptr(w, slot, WF_R_S6)->w = h.t;
+          rec_ptr(w, slot, WF_R_S8)->z = __uint_as_float(h.ref);
+        }
       } else {
         rec_st(w, slot, WF_R_H, make_float4(h.t, __uint_as_float(h.idx), __uint_as_float(h.ref), 0.0f));
         if (fix_class && lin_miss && h.idx != CRT_MAX_U32) w.cls[slot] = (uint8_t)0;   // WF_LIVE_CLASS: a triangle turned the miss into a hit
@@ -999,10 +1071,11 @@ cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* sh
                       int* trav_blocks_per_sm) {
   cudaError_t e;
 #define CRT_WF_CFG(S)                                                                                                              \
-  if ((e = cudaFuncSetAttribute(wf_logic<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaFuncSetAttribute(wf_logic<S, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaFuncSetAttribute(wf_logic<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
   if ((e = cudaFuncSetAttribute(wf_shade<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
   if ((e = cudaFuncSetAttribute(wf_regen<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
-  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<S>, WF_LOGIC_BLOCK, smem)) != cudaSuccess) return e; \
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<S, true>, WF_LOGIC_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(regen_blocks_per_sm, wf_regen<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaFuncSetAttribute(wf_tail<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;     \
@@ -1019,8 +1092,13 @@ cudaError_t launch_wf_begin(const WfState& w, const WfChunk& ck, cudaStream_t s)
 
 cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s) {
-  if (stats) wf_logic<true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
-  else wf_logic<false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
+  if (sc.shadow_closest) {
+    if (stats) wf_logic<true, true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
+    else wf_logic<false, true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
+  } else {
+    if (stats) wf_logic<true, false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
+    else wf_logic<false, false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
+  }
   return cudaGetLastError();
 }
 
@@ -1091,7 +1169,9 @@ cudaError_t wf_graph_build(const DevScene& sc, const WfState& w, bool stats, uin
   };
   {
     void* args[] = {(void*)&sc, (void*)&w, &it, &logic_mode, &counters};
-    e = add(stats ? (void*)wf_logic<true> : (void*)wf_logic<false>, dim3(grid_l), dim3(WF_LOGIC_BLOCK), smem, args);
+    void* f = sc.shadow_closest ? (stats ? (void*)wf_logic<true, true> : (void*)wf_logic<false, true>)
+                                : (stats ? (void*)wf_logic<true, false> : (void*)wf_logic<false, false>);
+    e = add(f, dim3(grid_l), dim3(WF_LOGIC_BLOCK), smem, args);
     if (e != cudaSuccess) { cudaGraphDestroy(g); return e; }
   }
   if (sc.n_tri) {

@@ -138,6 +138,32 @@ def soup_scene(width: int = 1920, height: int = 1080, n: int = 10_000_000, seed:
     return _with_triangles(base, 6, soup_triangles(n, seed))
 
 
+def with_triangle_lights(ps: PackedScene, tris: np.ndarray, emission: str = "light") -> PackedScene:
+    """``ps`` plus emitting triangles: each is appended to binding 8 (category 2, material light) and to binding 7 as a light
+    record (origin, edge1, edge2 as the reference's patch lights, MJ:255-296; data4 = (emission, 0, light, primitive index)).
+    An extension: the reference has one patch light.  Its shader samples a light's parallelogram origin + u e1 + v e2
+    (CS:341-355), so half of the samples towards a triangle light land beside it and contribute nothing -- the semantics as
+    written, which the oracle and the kernels share."""
+    t = np.asarray(tris, dtype="<f4")
+    k, n0, l0 = t.shape[0], ps.primitives.size, ps.lights.size
+    prims = np.zeros(n0 + k, dtype=PRIM_DTYPE)
+    prims.view(np.uint8)[: n0 * 80] = copy_records(ps.primitives).view(np.uint8)
+    lights = np.zeros(l0 + k, dtype=PRIM_DTYPE)
+    lights.view(np.uint8)[: l0 * 80] = copy_records(ps.lights).view(np.uint8)
+    e = ps.spectrum_index[emission]
+    for rec, sl in ((prims, slice(n0, n0 + k)), (lights, slice(l0, l0 + k))):
+        rec["category"][sl] = CATEGORY_TRIANGLE
+        rec["data1"][sl] = t[:, 0]
+        rec["data2"][sl] = t[:, 1] - t[:, 0]
+        rec["data3"][sl] = t[:, 2] - t[:, 0]
+        rec["data4"][sl, 0] = e
+        rec["data4"][sl, 1] = 0
+        rec["data4"][sl, 2] = 1  # light
+        rec["data4"][sl, 3] = np.arange(n0, n0 + k, dtype=np.uint32)
+    return PackedScene(width=ps.width, height=ps.height, planar_patches=copy_records(ps.planar_patches), camera=ps.camera.copy(), cie=ps.cie,
+                       spectra=ps.spectra, lights=lights, primitives=prims, spectrum_index=dict(ps.spectrum_index))
+
+
 def camera_rays(ps: PackedScene, n: int, seed: int = 0) -> np.ndarray:
     """n random rays (n x 8 f32: origin, -, direction, -) through the scene volume, for hit-parity tests.
 

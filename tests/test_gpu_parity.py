@@ -572,6 +572,50 @@ def test_adversarial_rays_bit_exact_vs_linear_scan(gpu, oracle):
     assert_radiance(acc, acc_c, 2)
 
 
+# ------------------------------------------------------------------------------------------------ triangle lights
+def _tri_light_scene(w, h):
+    ps = scenes.mesh_scene(w, h, n_lon=64, n_lat=32)
+    lights = np.array([[[60, 500, 120], [180, 500, 120], [60, 500, 260]],          # a triangle light under the ceiling, facing down
+                       [[400, 80, 100], [400, 80, 260], [400, 240, 100]]], dtype=np.float32)   # and one standing near the right wall
+    return scenes.with_triangle_lights(ps, lights)
+
+
+@pytest.mark.parametrize("tuning", [0, 16, (31 << 8), 16 | (31 << 8) | 2, 5 << 8], ids=["default", "host_loop", "no_tail", "host_routed_no_tail", "tail_16"])
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_triangle_lights_radiance_parity(gpu, oracle, kernel, tuning):
+    """A light that is itself a triangle: its shadow rays need CLOSEST-hit traversal (the linear list cannot find the light)
+    and the contribution can only be computed once the hit on the light is known.  Round 1 sent such scenes to the megakernel;
+    now the wavefront form carries the path too (a closest-hit mode of the shadow queue, the contribution rebuilt at the next
+    pass or inline in wf_tail) -- both forms against the oracle's linear scan, three lights (the reference's patch light and two
+    triangles), bit for bit, through the loop on the device, the host loop, with and without wf_tail."""
+    if kernel == 1 and tuning:
+        pytest.skip("wf_tuning does not apply to the megakernel")
+    ps = _tri_light_scene(112, 80)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    st = gpu.scene_stats()
+    assert st["shadow_closest"]
+    acc, fb, cg = _render(gpu, 4, kernel=kernel, max_depth=8, wf_slots=4096 if tuning else 0, wf_tuning=tuning)
+    acc_c, fb_c, cc = oracle.scene(ps, default_params(max_depth=8)).render(4)
+    assert_radiance(acc, acc_c, 4)
+    assert np.array_equal(fb, fb_c)
+    assert cg == (int(cc[0]), int(cc[1]), int(cc[2]))
+    # the triangle lights do light the scene: more radiance than with the patch light alone
+    ps0 = scenes.mesh_scene(112, 80, n_lon=64, n_lat=32)
+    acc0, _, _ = oracle.scene(ps0, default_params(max_depth=8)).render(4)
+    assert float(np.nansum(acc_c[..., 1])) != float(np.nansum(acc0[..., 1]))
+
+
+def test_triangle_lights_auto_uses_the_wavefront_form(gpu, oracle):
+    ps = _tri_light_scene(96, 64)
+    gpu.set_scene(ps); gpu.set_shard(0, 1, 0)
+    acc, fb, cg = _render(gpu, 3, max_depth=8)                   # AUTO
+    c = gpu.counters()
+    assert c["wf_iterations"] > 0                               # not the megakernel
+    acc_c, fb_c, cc = oracle.scene(ps, default_params(max_depth=8)).render(3)
+    assert_radiance(acc, acc_c, 3)
+    assert np.array_equal(fb, fb_c)
+
+
 # ------------------------------------------------------------------------------------------------ single-process group
 @pytest.mark.parametrize("mode", [SHARD_TILES, SHARD_SPLIT_SPP], ids=["tiles", "split_spp"])
 @pytest.mark.parametrize("n", [2, 3])

@@ -37,6 +37,18 @@ def main():
                 ref = acc
             assert np.array_equal(acc[..., :3].view(np.uint32), ref[..., :3].view(np.uint32)), name
             print("ok:", name, flush=True)
+        lights = np.array([[[60, 500, 120], [180, 500, 120], [60, 500, 260]]], dtype=np.float32)
+        r.set_scene(scenes.with_triangle_lights(ps, lights))
+        tri_ref = None
+        for name, kw in (("triangle light, wavefront", dict(kernel=KERNEL_WAVEFRONT, wf_slots=2048, wf_tuning=5 << 8)), ("triangle light, megakernel", dict(kernel=KERNEL_MEGA))):
+            r.set_params(default_params(max_depth=8, **kw)); r.reset()
+            r.frame(3)
+            acc = r.accumulator()
+            if tri_ref is None:
+                tri_ref = acc
+            assert np.array_equal(acc[..., :3].view(np.uint32), tri_ref[..., :3].view(np.uint32)), name
+            print("ok:", name, flush=True)
+        r.set_scene(ps); r.set_params(default_params(max_depth=8))
         rays = scenes.camera_rays(ps, 2048, seed=1)
         idx, t = r.trace_rays(rays)
         print("ok: trace_rays", int((idx >= 6).sum()), "triangle hits", flush=True)
