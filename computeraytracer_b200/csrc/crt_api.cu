@@ -741,6 +741,61 @@ int group_combine(crt_ctx* g) {
 
 }  // namespace
 
+// ------------------------------------------------------------------------------------------------ crt_trace_rays_noalloc
+// Scratch of the allocation-free trace_rays variant: the device-side staging that crt_trace_rays takes from cudaMalloc, as a
+// file-scope array of a fixed, modest size -- CRT_NOALLOC_MAX_RAYS x (32 B ray + 4 B exclude + 4 B hit index + 4 B t) = 2.75 MiB,
+// held by every GPU that loads the library until the process exits.  In host code the name below is only a stand-in for the
+// symbol, not a device address: the entry point resolves it with cudaGetSymbolAddress once per device (noalloc_scratch_of) and
+// hands the kernel that pointer.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[(size_t)CRT_NOALLOC_MAX_RAYS * 44u];
+
+namespace {
+constexpr size_t kNoallocRays = 0;                                            // float4[2 n_max]
+constexpr size_t kNoallocExcl = (size_t)CRT_NOALLOC_MAX_RAYS * 32u;           // uint32[n_max]
+constexpr size_t kNoallocIdx = kNoallocExcl + (size_t)CRT_NOALLOC_MAX_RAYS * 4u;
+constexpr size_t kNoallocT = kNoallocIdx + (size_t)CRT_NOALLOC_MAX_RAYS * 4u;
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mutex;                       // calls share the array: within a process they are serialised here
+void* g_noalloc_ptr[kNoallocMaxDevices] = {};     // device address of g_noalloc_scratch on each device, resolved on first use
+
+// `device` must be current.  No allocation: the array exists as soon as the module is loaded on the device.
+cudaError_t noalloc_scratch_of(int device, unsigned char** out) {
+  if (device < 0 || device >= kNoallocMaxDevices) return cudaErrorInvalidDevice;
+  if (!g_noalloc_ptr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    g_noalloc_ptr[device] = p;
+  }
+  *out = (unsigned char*)g_noalloc_ptr[device];
+  return cudaSuccess;
+}
+}  // namespace
+
+// trace_rays_kernel (crt_kernels.cu) with inputs and outputs in the scratch array: intersect() (CS:503-518) per ray, the same
+// device code, so hit index and t are those of crt_trace_rays bit for bit.
+__global__ void trace_rays_scratch_kernel(const __grid_constant__ DevScene sc, unsigned char* __restrict__ scratch, uint32_t n, uint32_t has_exclude,
+                                          unsigned long long* __restrict__ counters) {
+  const float4* rays = reinterpret_cast<const float4*>(scratch + kNoallocRays);
+  const uint32_t* exclude = reinterpret_cast<const uint32_t*>(scratch + kNoallocExcl);
+  uint32_t* hit_idx = reinterpret_cast<uint32_t*>(scratch + kNoallocIdx);
+  float* t_out = reinterpret_cast<float*>(scratch + kNoallocT);
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  Stats st; st.prim_tests = st.node_visits = st.tri_tests = st.rand_calls = 0;
+  if (i < n) {
+    const float4 o = rays[2 * i], d = rays[2 * i + 1];
+    const Hit h = intersect<true>(sc, v3(o), v3(d), has_exclude ? exclude[i] : CRT_MAX_U32, st);
+    hit_idx[i] = h.idx;
+    t_out[i] = h.t;
+  }
+  unsigned long long v[3] = {st.prim_tests, st.node_visits, st.tri_tests};
+  for (int k = 0; k < 3; k++) {
+    unsigned long long x = v[k];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    if ((threadIdx.x & 31u) == 0 && x) atomicAdd(&counters[CRT_CNT_PRIM_TESTS + k], x);
+  }
+}
+
 extern "C" {
 
 const char* crt_version(void) { return CRT_VERSION_STRING; }
@@ -1276,6 +1331,41 @@ int crt_trace_rays(crt_ctx* ctx, const float* rays, const uint32_t* exclude, siz
   CU(crt::launch_trace_rays(ctx->scene, d_rays.as<float4>(), d_ex.as<uint32_t>(), (uint32_t)n, d_idx.as<uint32_t>(), d_t.as<float>(), ctx->d_counters, ctx->stream));
   CU(cudaMemcpyAsync(hit_idx, d_idx.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaMemcpyAsync(t, d_t.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return CRT_OK;
+}
+
+// crt_trace_rays without any allocation (no counterpart in the reference): for
+// callers that cannot call cudaMalloc -- code under CUDA-graph capture, tight serving loops, harnesses that forbid it.  Same
+// inputs, outputs and results as crt_trace_rays; the device-side staging lives in g_noalloc_scratch.  It cannot run the
+// scene-upload module either (that allocates), so the scene must be resident already.
+int crt_trace_rays_noalloc(crt_ctx* ctx, const float* rays, const uint32_t* exclude, size_t n, uint32_t* hit_idx, float* t) {
+  if (!ctx || (!rays && n) || (!hit_idx && n) || (!t && n)) return CRT_ERR_ARG;
+  if (is_group(ctx)) return group_fail(ctx, ctx->members[0], crt_trace_rays_noalloc(ctx->members[0], rays, exclude, n, hit_idx, t));
+  if (n > CRT_NOALLOC_MAX_RAYS)
+    return fail(ctx, CRT_ERR_SIZE, "crt_trace_rays_noalloc takes at most %u rays per call (its scratch is a fixed array), got %zu: split the batch or use crt_trace_rays",
+                (unsigned)CRT_NOALLOC_MAX_RAYS, n);
+  for (int b = 4; b <= 8; b++)
+    if (!ctx->have[b]) return fail(ctx, CRT_ERR_STATE, "binding %d has not been set", b);
+  if (ctx->camera_dirty || ctx->tables_dirty || ctx->scene_dirty)
+    return fail(ctx, CRT_ERR_STATE, "the scene is not resident yet (a binding changed since the last upload): this entry point allocates nothing and so cannot "
+                                    "run the scene-upload module -- call crt_scene_stats, crt_dispatch_frames or crt_trace_rays once first");
+  CU(cudaSetDevice(ctx->device));
+  if (!n) return CRT_OK;
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);   // every call shares the array
+  unsigned char* scratch = nullptr;
+  CU(noalloc_scratch_of(ctx->device, &scratch));
+  DevScene sc = ctx->scene;                            // as prepare() leaves it, with the current parameters
+  sc.max_depth = ctx->params.max_depth; sc.grid_size = ctx->params.grid_size ? ctx->params.grid_size : 1;
+  sc.t_min = ctx->params.t_min; sc.exposure = ctx->params.exposure;
+  sc.rank = ctx->rank; sc.world = ctx->world; sc.shard_mode = ctx->shard_mode;
+  // nothing in the array has to start at zero: the kernel writes hit_idx[i] and t[i] for every i < n and reads nothing else back
+  CU(cudaMemcpyAsync(scratch + kNoallocRays, rays, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+  if (exclude) CU(cudaMemcpyAsync(scratch + kNoallocExcl, exclude, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  trace_rays_scratch_kernel<<<((unsigned)n + 127u) / 128u, 128, 0, ctx->stream>>>(sc, scratch, (uint32_t)n, exclude ? 1u : 0u, ctx->d_counters);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(hit_idx, scratch + kNoallocIdx, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaMemcpyAsync(t, scratch + kNoallocT, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   return CRT_OK;
 }

@@ -42,6 +42,7 @@ WF_DEFER_OFF, WF_DEFER_ON, WF_HOST_LOOP = 4, 8, 16
 WF_TAIL_SHIFT, WF_TAIL_OFF = 8, 31 << 8   # bits 8-12: v = 1..30 -> wf_tail takes over at <= 2^(v-1) live slots; 31: never
 BVH_EXACT_SLOTS, BVH_BUILDER_HOST_SAH, BVH_BUILDER_DEVICE = 0x200, 0x400, 0x800
 COMM_ID_BYTES = 128
+NOALLOC_MAX_RAYS = 65536   # CRT_NOALLOC_MAX_RAYS
 
 STATUS = {0: "CRT_OK", 1: "CRT_ERR_ARG", 2: "CRT_ERR_BINDING", 3: "CRT_ERR_SIZE", 4: "CRT_ERR_STATE",
           5: "CRT_ERR_CUDA", 6: "CRT_ERR_OOM", 7: "CRT_ERR_NODEVICE", 8: "CRT_ERR_NCCL"}
@@ -96,6 +97,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     lib.crt_stream.argtypes = [vp, C.POINTER(vp)]
     lib.crt_set_stream.argtypes = [vp, vp]
     lib.crt_trace_rays.argtypes = [vp, vp, vp, sz, vp, vp]
+    lib.crt_trace_rays_noalloc.argtypes = [vp, vp, vp, sz, vp, vp]
     lib.crt_get_counters.argtypes = [vp, vp, sz]
     lib.crt_reset_counters.argtypes = [vp]
     lib.crt_get_kernel_times.argtypes = [vp, vp, vp, sz]
@@ -296,6 +298,18 @@ class Renderer:
         ex = None if exclude is None else np.ascontiguousarray(exclude, dtype=np.uint32)
         self._ck(self.lib.crt_trace_rays(self.h, rays.ctypes.data, ex.ctypes.data if ex is not None else None, n,
                                          idx.ctypes.data, t.ctypes.data))
+        return idx, t
+
+    def trace_rays_noalloc(self, rays: np.ndarray, exclude: Optional[np.ndarray] = None):
+        """``crt_trace_rays_noalloc``: as :meth:`trace_rays`, but the call allocates nothing on the device (at most
+        ``NOALLOC_MAX_RAYS`` rays; the scene must be resident)."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        n = rays.shape[0]
+        idx = np.empty(n, dtype=np.uint32)
+        t = np.empty(n, dtype=np.float32)
+        ex = None if exclude is None else np.ascontiguousarray(exclude, dtype=np.uint32)
+        self._ck(self.lib.crt_trace_rays_noalloc(self.h, rays.ctypes.data, ex.ctypes.data if ex is not None else None, n,
+                                                 idx.ctypes.data, t.ctypes.data))
         return idx, t
 
     def counters(self) -> dict:

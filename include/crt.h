@@ -238,6 +238,21 @@ CRT_API int crt_set_stream(crt_ctx* ctx, void* cuda_stream);
 CRT_API int crt_trace_rays(crt_ctx* ctx, const float* rays, const uint32_t* exclude, size_t n,
                            uint32_t* hit_idx, float* t);
 
+/* crt_trace_rays for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA-graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same arguments, same results (hit
+ * index and t bit for bit) as crt_trace_rays, but the call makes no cudaMalloc / cudaFree and calls no allocating library routine:
+ * the device-side staging of rays and results is a file-scope static __device__ array inside the library, sized for
+ * CRT_NOALLOC_MAX_RAYS rays (2.75 MiB, held by every GPU that loads the library until the process exits).
+ *   - n > CRT_NOALLOC_MAX_RAYS is rejected with CRT_ERR_SIZE (split the batch, or use crt_trace_rays);
+ *   - the scene must be resident already (the scene-upload module allocates): CRT_ERR_STATE if a binding has been set since the last
+ *     crt_dispatch_frames / crt_scene_stats / crt_trace_rays;
+ *   - every call on a device shares the one array, which keeps the previous call's contents; nothing in it has to start at zero
+ *     (each call overwrites what it reads back).  Calls are serialised within a process and synchronise before returning; calls
+ *     that would overlap on the GPU some other way (several processes each hold their own copy, so that is not one) would race. */
+#define CRT_NOALLOC_MAX_RAYS 65536u
+CRT_API int crt_trace_rays_noalloc(crt_ctx* ctx, const float* rays, const uint32_t* exclude, size_t n,
+                                   uint32_t* hit_idx, float* t);
+
 /* Device-side counters accumulated since the last crt_reset_counters (enum crt_counter). */
 CRT_API int crt_get_counters(crt_ctx* ctx, uint64_t* out, size_t n);
 CRT_API int crt_reset_counters(crt_ctx* ctx);
