@@ -210,9 +210,11 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------ B200 arm
 def time_steps(r, stream, torch, steps, frames, flush_buf, combine):
     """K steps, each bracketed by its own CUDA events on the renderer's stream; L2 flushed between steps.  A step is the
-    frames plus -- on more than one GPU -- the combine (collective + rank 0's tone-map), all enqueued asynchronously."""
+    frames plus -- on more than one GPU -- the combine (collective + rank 0's tone-map), all enqueued asynchronously: the host
+    does not wait between steps (the combine is timed by events of its own on the same stream), so the K steps are one
+    stream of work between the caller's barriers, as the contract states it."""
     evs = []
-    comb = []
+    cevs = []
     for _ in range(steps):
         if flush_buf is not None:
             with torch.cuda.stream(stream):
@@ -221,13 +223,18 @@ def time_steps(r, stream, torch, steps, frames, flush_buf, combine):
         e0.record(stream)
         r.frame(frames)
         if combine:
+            c0 = torch.cuda.Event(enable_timing=True)
+            c0.record(stream)
             r.combine(0)
         e1.record(stream)
         evs.append((e0, e1))
         if combine:
-            stream.synchronize()                  # crt_last_combine reads the most recent combine's events
-            comb.append(r.last_combine())
+            cevs.append((c0, e1))
     stream.synchronize()
+    comb = []
+    if combine:
+        nbytes = r.last_combine()[1]              # the same every step
+        comb = [(a.elapsed_time(b), nbytes) for a, b in cevs]
     return [a.elapsed_time(b) for a, b in evs], comb
 
 
