@@ -50,7 +50,8 @@ struct crt_ctx {
   bool have[9] = {false, false, false, false, false, false, false, false, false};
   bool scene_dirty = true, tables_dirty = true, camera_dirty = true;
   std::shared_ptr<const crt::BvhResult> host_bvh;   // host-built tree of b_prims (a group builds it once)
-  const void* host_bvh_for = nullptr;
+  std::shared_ptr<const std::vector<uint8_t>> host_bvh_for;   // the binding-8 bytes the cached tree was built from (held, so that
+                                                                // a later scene cannot be allocated at the same address and match)
   uint32_t host_bvh_tuning = 0; float host_bvh_prim_cost = 0.0f;
 
   crt_params params;
@@ -88,6 +89,15 @@ struct crt_ctx {
   cudaGraph_t wf_graph = nullptr;    // the iteration loop as a CUDA-graph WHILE node, rebuilt when its key changes
   cudaGraphExec_t wf_graph_exec = nullptr;
   std::vector<uint8_t> wf_graph_key;
+  // second lane (dispatch_wavefront: a chunk's samples are split over two half pools that run side by side on two streams)
+  WfState wf2;
+  void* wf2_mem = nullptr;
+  uint32_t wf2_slots = 0;
+  cudaGraph_t wf2_graph = nullptr;
+  cudaGraphExec_t wf2_graph_exec = nullptr;
+  std::vector<uint8_t> wf2_graph_key;
+  cudaStream_t lane_stream[2] = {nullptr, nullptr};
+  cudaEvent_t lane_fork = nullptr, lane_join[2] = {nullptr, nullptr};
   std::vector<float4> slow_log;
 
   // CRT_FLAG_KERNEL_TIMES: events recorded between consecutive hot-path launches
@@ -354,14 +364,14 @@ int upload_scene(crt_ctx* ctx) {
     }
   }
   if (s.n_tri && !built_on_device) {
-    if (!ctx->host_bvh || ctx->host_bvh_for != (const void*)ctx->b_prims.get() || ctx->host_bvh_tuning != ctx->params.bvh_tuning ||
+    if (!ctx->host_bvh || ctx->host_bvh_for != ctx->b_prims || ctx->host_bvh_tuning != ctx->params.bvh_tuning ||
         ctx->host_bvh_prim_cost != ctx->params.bvh_prim_cost) {
       auto bvh = std::make_shared<crt::BvhResult>();
       const int threads = (int)std::max(1u, std::thread::hardware_concurrency());
       const auto b0 = std::chrono::steady_clock::now();
       crt::build_bvh(prims, tri_pos, threads, crt::bvh_options(ctx->params.bvh_tuning, ctx->params.bvh_prim_cost), *bvh);
       bvh->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - b0).count();
-      ctx->host_bvh = bvh; ctx->host_bvh_for = ctx->b_prims.get();
+      ctx->host_bvh = bvh; ctx->host_bvh_for = ctx->b_prims;
       ctx->host_bvh_tuning = ctx->params.bvh_tuning; ctx->host_bvh_prim_cost = ctx->params.bvh_prim_cost;
     }
     const crt::BvhResult& bvh = *ctx->host_bvh;
@@ -434,23 +444,33 @@ int prepare(crt_ctx* ctx) {
 
 constexpr size_t kWfCounterBytes = (size_t)(CRT_WF_MAX_ITERS + 2) * sizeof(WfIter) + 64;   // iteration records + the work counter
 
-int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
-  ctx->wf.slow_min = ctx->params.slow_ray_nodes;   // diagnostics: log rays that visit at least this many nodes (stats mode)
-  if (ctx->wf_mem && ctx->wf_slots >= n_slots) return CRT_OK;
+// the per-lane wavefront state: lane 0 is the pool every form uses, lane 1 the second half pool of the two-lane device loop
+struct LaneRef {
+  WfState* wf; void** mem; uint32_t* slots; cudaGraph_t* graph; cudaGraphExec_t* exec; std::vector<uint8_t>* key;
+};
+LaneRef lane_of(crt_ctx* ctx, int h) {
+  if (h == 0) return LaneRef{&ctx->wf, &ctx->wf_mem, &ctx->wf_slots, &ctx->wf_graph, &ctx->wf_graph_exec, &ctx->wf_graph_key};
+  return LaneRef{&ctx->wf2, &ctx->wf2_mem, &ctx->wf2_slots, &ctx->wf2_graph, &ctx->wf2_graph_exec, &ctx->wf2_graph_key};
+}
+
+int ensure_wavefront(crt_ctx* ctx, int h, uint32_t n_slots) {
+  const LaneRef L = lane_of(ctx, h);
+  WfState& w = *L.wf;
+  w.slow_min = h == 0 ? ctx->params.slow_ray_nodes : 0u;   // diagnostics: log rays that visit at least this many nodes (stats mode)
+  if (*L.mem && *L.slots >= n_slots) return CRT_OK;
   uint32_t iters_total = 0, launches_total = 0;
-  if (ctx->wf_mem) {   // keep the device-side iteration / launch counts across a pool that grows
+  if (*L.mem) {   // keep the device-side iteration / launch counts across a pool that grows
     uint32_t tmp[4];
-    CU(cudaMemcpy(tmp, ctx->wf.ctl, 16, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(tmp, w.ctl, 16, cudaMemcpyDeviceToHost));
     iters_total = tmp[2]; launches_total = tmp[3];
-    cudaFree(ctx->wf_mem); ctx->wf_mem = nullptr;
+    cudaFree(*L.mem); *L.mem = nullptr;
   }
   // one record per slot; shade and finish queues of two iterations, the regen queue, the BVH queue (2 entries per slot)
   const size_t slow_bytes = (size_t)(1 + 3 * CRT_WF_SLOW_RAYS) * 16;
   const size_t cls_bytes = ((size_t)n_slots + 255) & ~(size_t)255;
   const size_t total = (size_t)(CRT_WF_REC_WORDS * 16 + 7 * 4) * n_slots + kWfCounterBytes + 256 + slow_bytes + cls_bytes + 256;
-  CU(cudaMalloc(&ctx->wf_mem, total));
-  uint8_t* p = (uint8_t*)ctx->wf_mem;
-  WfState& w = ctx->wf;
+  CU(cudaMalloc(L.mem, total));
+  uint8_t* p = (uint8_t*)*L.mem;
   w.rec = (float4*)p; p += (size_t)CRT_WF_REC_WORDS * 16 * n_slots;
   w.bounce[0] = (uint32_t*)p; p += 4 * (size_t)n_slots;
   w.bounce[1] = (uint32_t*)p; p += 4 * (size_t)n_slots;
@@ -468,16 +488,28 @@ int ensure_wavefront(crt_ctx* ctx, uint32_t n_slots) {
   const uint32_t init[4] = {0u, 0u, iters_total, launches_total};
   CU(cudaMemset(w.ctl, 0, sizeof(WfCtl)));
   CU(cudaMemcpy(w.ctl, init, 16, cudaMemcpyHostToDevice));
-  ctx->wf_slots = n_slots;
+  *L.slots = n_slots;
   if (!ctx->wf_host_count) CU(cudaMallocHost(&ctx->wf_host_count, 16));
   return CRT_OK;
 }
 
-void drop_wf_graph(crt_ctx* ctx) {
+void drop_wf_graph(crt_ctx* ctx, int h) {
+  const LaneRef L = lane_of(ctx, h);
   // (an executable graph that is still running is released by the runtime when it completes)
-  if (ctx->wf_graph_exec) { cudaGraphExecDestroy(ctx->wf_graph_exec); ctx->wf_graph_exec = nullptr; }
-  if (ctx->wf_graph) { cudaGraphDestroy(ctx->wf_graph); ctx->wf_graph = nullptr; }
-  ctx->wf_graph_key.clear();
+  if (*L.exec) { cudaGraphExecDestroy(*L.exec); *L.exec = nullptr; }
+  if (*L.graph) { cudaGraphDestroy(*L.graph); *L.graph = nullptr; }
+  L.key->clear();
+}
+
+// streams and events of the two-lane device loop, created on first use
+int ensure_lanes(crt_ctx* ctx) {
+  if (ctx->lane_fork) return CRT_OK;
+  for (int h = 0; h < 2; h++) {
+    CU(cudaStreamCreateWithFlags(&ctx->lane_stream[h], cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&ctx->lane_join[h], cudaEventDisableTiming));
+  }
+  CU(cudaEventCreateWithFlags(&ctx->lane_fork, cudaEventDisableTiming));
+  return CRT_OK;
 }
 
 // n frames as a wavefront, in chunks.  Iteration 0 starts a path on every slot; every later iteration is one pass of
@@ -552,15 +584,41 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       ck.s_first = ctx->sample + 1u; ck.s_stride = 1u; ck.n_samples = k;
     }
     const uint64_t total_work = (uint64_t)n_units * ck.n_samples;
-    // slots for this chunk: all of its work items when they are few, the pool when they are many, and in between half of the
+    // Two lanes (device loop only): the chunk's samples are split in two halves that run side by side, each over its own half
+    // pool, control block and graph, on two streams forked from and joined into the context's stream.  Every launch of
+    // wf_traverse ends in a straggler phase -- the rays with the longest chains of dependent fetches (155 nodes on mesh1m)
+    // finish 0.3-0.4 ms after the bulk, with the SMs mostly idle (profiles/r02_launches_mesh1m.csv: late iterations take
+    // 340-430 us in wf_traverse against 50-150 us in wf_logic) -- and a chunk ends in thin iterations and wf_tail; with two
+    // lanes the other half's kernels fill the machine meanwhile.  Samples are staged by work item and summed in frame order
+    // afterwards, so the split changes no bit.
+    // (Measured, profiles/r02m_two_lanes_ab.txt: mesh1m 256-spp step 325.5 -> 318.4 ms, 32-frame step 43.7 -> 42.0, 8-frame 13.1 ->
+    // 12.3, Cornell 53.2 -> 51.1; the 10M soup, whose 650 MB scene streams from HBM, loses 2 % with two traversals competing
+    // for it -- scenes larger than L2 keep one lane.)
+    const bool fits_l2 = ctx->scene_bytes <= (96ull << 20);
+    const bool two_lanes = !host_loop && !(ctx->params.wf_tuning & CRT_WF_ONE_LANE) && !ctx->params.slow_ray_nodes && ck.n_samples >= 2 &&
+                           ((total_work >= (4ull << 20) && fits_l2) || (ctx->params.wf_tuning & CRT_WF_TWO_LANES_ALWAYS));
+    const int n_parts = two_lanes ? 2 : 1;
+    const uint64_t lane_pool = two_lanes ? std::max<uint64_t>(pool / 2, 32) : pool;
+    WfChunk part[2] = {ck, ck};
+    if (two_lanes) {
+      part[0].n_samples = (ck.n_samples + 1u) / 2u;
+      part[1].n_samples = ck.n_samples - part[0].n_samples;
+      part[1].s_first = ck.s_first + part[0].n_samples * ck.s_stride;
+    }
+    // slots per part: all of its work items when they are few, the pool when they are many, and in between half of the
     // items -- a chunk of one to two pools' worth (what a rank renders per step when eight GPUs share 256 spp) is 3 % faster
     // when every slot regenerates once (a finish pass shared with the next path's start) than with one path per slot
     // (profiles/r02g_pool_coherence_ab.txt: 32-frame step 44.5 -> 43.2 ms).  An explicit crt_params.wf_slots is taken as given.
-    uint64_t want_slots = std::min<uint64_t>(std::max<uint64_t>(total_work, 32), pool);
-    if (!ctx->params.wf_slots && total_work > (16ull << 20)) want_slots = std::min<uint64_t>(std::max<uint64_t>(total_work / 2, 16ull << 20), pool);
-    ck.n_slots = (uint32_t)want_slots;
-    // worst case: every slot runs ceil(total/slots) paths of `worst` iterations one after the other
-    const uint64_t iters_worst = worst * ((total_work + ck.n_slots - 1) / ck.n_slots + 1) + 2;
+    uint64_t iters_worst = 0;
+    for (int h = 0; h < n_parts; h++) {
+      const uint64_t work_h = (uint64_t)n_units * part[h].n_samples;
+      uint64_t want_slots = std::min<uint64_t>(std::max<uint64_t>(work_h, 32), lane_pool);
+      if (!ctx->params.wf_slots && work_h > (16ull << 20)) want_slots = std::min<uint64_t>(std::max<uint64_t>(work_h / 2, 16ull << 20), lane_pool);
+      part[h].n_slots = (uint32_t)want_slots;
+      // worst case: every slot runs ceil(work/slots) paths of `worst` iterations one after the other
+      iters_worst = std::max<uint64_t>(iters_worst, worst * ((work_h + part[h].n_slots - 1) / part[h].n_slots + 1) + 2);
+    }
+    ck.n_slots = part[0].n_slots;
     if (iters_worst > CRT_WF_MAX_ITERS && k > 1) {   // shrink the chunk so the per-iteration counters cannot run out
       chunk = std::max(1u, k / 2);
       continue;
@@ -572,32 +630,56 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
       ctx->wf_stage_bytes = stage_bytes;
     }
     ck.stage = (float4*)ctx->wf_stage;
+    part[0].stage = ck.stage;
+    part[1].stage = ck.stage + (size_t)part[0].n_samples * n_units;   // staged by (sample ordinal, unit): the second half follows the first
     if (ck.n_samples && n_units) {
-      int rc = ensure_wavefront(ctx, ck.n_slots);
-      if (rc) return rc;
-      CU(cudaMemsetAsync(ctx->wf.iter, 0, kWfCounterBytes, ctx->stream));
-      CU(crt::launch_wf_begin(ctx->wf, ck, ctx->stream));
       if (!host_loop) {
         // ---- the loop runs on the device
-        struct Key { DevScene sc; WfState w; uint32_t stats, logic_mode, live_mode, tail_max; int gl, gt, gp; size_t smem; void* counters; };
-        static_assert(std::is_trivially_copyable<Key>::value, "graph key");
-        std::vector<uint8_t> key(sizeof(Key), 0);
-        {
-          Key kk; memset((void*)&kk, 0, sizeof(kk));
-          kk.sc = s; kk.w = ctx->wf; kk.stats = stats; kk.logic_mode = logic_mode; kk.live_mode = live_mode; kk.tail_max = tail_max;
-          kk.gl = grid_l; kk.gt = grid_t; kk.gp = grid_p; kk.smem = smem; kk.counters = ctx->d_counters;
-          memcpy(key.data(), &kk, sizeof(kk));
+        if (two_lanes) {
+          int rc = ensure_lanes(ctx);
+          if (rc) return rc;
+          CU(cudaEventRecord(ctx->lane_fork, ctx->stream));
         }
-        if (!ctx->wf_graph_exec || key != ctx->wf_graph_key) {
-          drop_wf_graph(ctx);
-          CU(crt::wf_graph_build(s, ctx->wf, stats, logic_mode, live_mode, grid_l, grid_t, grid_p, smem, ctx->d_counters, kernels_per_iter, tail_max,
-                                 &ctx->wf_graph, &ctx->wf_graph_exec));
-          ctx->wf_graph_key = key;
+        for (int h = 0; h < n_parts; h++) {
+          const LaneRef L = lane_of(ctx, h);
+          cudaStream_t st = two_lanes ? ctx->lane_stream[h] : ctx->stream;
+          int rc = ensure_wavefront(ctx, h, part[h].n_slots);
+          if (rc) return rc;
+          WfState& w = *L.wf;
+          w.tables_in_smem = ctx->wf.tables_in_smem;
+          if (two_lanes) CU(cudaStreamWaitEvent(st, ctx->lane_fork, 0));
+          CU(cudaMemsetAsync(w.iter, 0, kWfCounterBytes, st));
+          CU(crt::launch_wf_begin(w, part[h], st));
+          ctx->launches++;
+          struct Key { DevScene sc; WfState w; uint32_t stats, logic_mode, live_mode, tail_max; int gl, gt, gp; size_t smem; void* counters; };
+          static_assert(std::is_trivially_copyable<Key>::value, "graph key");
+          std::vector<uint8_t> key(sizeof(Key), 0);
+          {
+            Key kk; memset((void*)&kk, 0, sizeof(kk));
+            kk.sc = s; kk.w = w; kk.stats = stats; kk.logic_mode = logic_mode; kk.live_mode = live_mode; kk.tail_max = tail_max;
+            kk.gl = grid_l; kk.gt = grid_t; kk.gp = grid_p; kk.smem = smem; kk.counters = ctx->d_counters;
+            memcpy(key.data(), &kk, sizeof(kk));
+          }
+          if (!*L.exec || key != *L.key) {
+            drop_wf_graph(ctx, h);
+            CU(crt::wf_graph_build(s, w, stats, logic_mode, live_mode, grid_l, grid_t, grid_p, smem, ctx->d_counters, kernels_per_iter, tail_max,
+                                   L.graph, L.exec));
+            *L.key = key;
+          }
+          CU(cudaGraphLaunch(*L.exec, st));
+          if (tail_max) { CU(crt::launch_wf_tail(s, w, stats, live_mode, grid_tail, smem, CRT_WF_IT_DEVICE, ctx->d_counters, st)); ctx->launches++; }
+          if (two_lanes) {
+            CU(cudaEventRecord(ctx->lane_join[h], st));
+            CU(cudaStreamWaitEvent(ctx->stream, ctx->lane_join[h], 0));
+          }
         }
-        CU(cudaGraphLaunch(ctx->wf_graph_exec, ctx->stream));
-        if (tail_max) { CU(crt::launch_wf_tail(s, ctx->wf, stats, live_mode, grid_tail, smem, CRT_WF_IT_DEVICE, ctx->d_counters, ctx->stream)); ctx->launches++; }
       } else {
         // ---- the host launches every iteration
+        int rc = ensure_wavefront(ctx, 0, ck.n_slots);
+        if (rc) return rc;
+        CU(cudaMemsetAsync(ctx->wf.iter, 0, kWfCounterBytes, ctx->stream));
+        CU(crt::launch_wf_begin(ctx->wf, ck, ctx->stream));
+        ctx->launches++;
         uint32_t it = 0;
         uint32_t next_check = (ctx->wf_last_iters > 4 && ctx->wf_last_work == total_work) ? ctx->wf_last_iters - 1 : (uint32_t)(2 * (total_work / ck.n_slots) + 2);
         for (;;) {
@@ -648,7 +730,6 @@ int dispatch_wavefront(crt_ctx* ctx, uint32_t n, uint32_t n_units, bool stats) {
         ctx->wf_last_work = total_work;
         ctx->wf_iterations += it;
       }
-      ctx->launches++;   // wf_begin
     }
     ctx->sample += k;   // UpdateVariables.wgsl:3-8, once per frame
     CU(mark(ctx, CRT_KC_WF_ACCUMULATE));
@@ -833,6 +914,7 @@ int crt_create(int device, crt_ctx** out) {
   crt_default_params(&ctx->params);
   memset((void*)&ctx->scene, 0, sizeof(ctx->scene));
   memset((void*)&ctx->wf, 0, sizeof(ctx->wf));
+  memset((void*)&ctx->wf2, 0, sizeof(ctx->wf2));
   if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&ctx->ev_start) != cudaSuccess || cudaEventCreate(&ctx->ev_stop) != cudaSuccess ||
       cudaMalloc(&ctx->d_work, 4) != cudaSuccess || cudaMalloc(&ctx->d_counters, CRT_NUM_COUNTERS * 8) != cudaSuccess ||
@@ -885,7 +967,13 @@ void crt_destroy(crt_ctx* ctx) {
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   if (ctx->nccl_comm) { if (NcclApi* nc = nccl_api()) nc->CommDestroy(ctx->nccl_comm); ctx->nccl_comm = nullptr; }
-  drop_wf_graph(ctx);
+  drop_wf_graph(ctx, 0); drop_wf_graph(ctx, 1);
+  for (int h = 0; h < 2; h++) {
+    if (ctx->lane_stream[h]) cudaStreamDestroy(ctx->lane_stream[h]);
+    if (ctx->lane_join[h]) cudaEventDestroy(ctx->lane_join[h]);
+  }
+  if (ctx->lane_fork) cudaEventDestroy(ctx->lane_fork);
+  if (ctx->wf2_mem) cudaFree(ctx->wf2_mem);
   dfree(ctx->d_acc); dfree(ctx->d_fb); dfree(ctx->d_tea); dfree(ctx->d_cam); dfree(ctx->d_spectra); dfree(ctx->d_cie);
   dfree(ctx->d_lin); dfree(ctx->d_lights); dfree(ctx->d_light_mask); dfree(ctx->d_nodes); dfree(ctx->d_work); dfree(ctx->d_counters);
   dfree(ctx->d_comb); dfree(ctx->d_xfer);
@@ -1239,11 +1327,11 @@ int crt_combine(crt_ctx* ctx, uint32_t dst) {
   if (rc) return rc;
   if ((rc = ensure_comb(ctx))) return rc;
   const size_t n_pix = ctx->acc_pixels;
+  if (dst >= ctx->world) return fail(ctx, CRT_ERR_ARG, "destination rank %u of %u", dst, ctx->world);
   if (ctx->world <= 1) {   // nothing to exchange: the combined image is the accumulator
     ctx->comb_valid = false; ctx->comb_bytes = 0; ctx->comb_timed = false;
     return crt_resolve_framebuffer(ctx);
   }
-  if (dst >= ctx->world) return fail(ctx, CRT_ERR_ARG, "destination rank %u of %u", dst, ctx->world);
   if (!ctx->nccl_comm) return fail(ctx, CRT_ERR_STATE, "no communicator: call crt_comm_init first");
   NcclApi* nc = nccl_api();
   if (!nc) return fail(ctx, CRT_ERR_NCCL, "NCCL is not available");
@@ -1394,9 +1482,12 @@ int crt_get_counters(crt_ctx* ctx, uint64_t* out, size_t n) {
   unsigned long long tmp[CRT_NUM_COUNTERS];
   uint32_t ctl[4] = {0, 0, 0, 0};
   CU(cudaMemcpyAsync(tmp, ctx->d_counters, sizeof(tmp), cudaMemcpyDeviceToHost, ctx->stream));
+  uint32_t ctl2[4] = {0, 0, 0, 0};
   if (ctx->wf_mem) CU(cudaMemcpyAsync(ctl, ctx->wf.ctl, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  if (ctx->wf2_mem) CU(cudaMemcpyAsync(ctl2, ctx->wf2.ctl, 16, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
-  if (ctl[1]) return fail(ctx, CRT_ERR_STATE, "wavefront iteration limit reached on the device");
+  if (ctl[1] || ctl2[1]) return fail(ctx, CRT_ERR_STATE, "wavefront iteration limit reached on the device");
+  ctl[2] += ctl2[2]; ctl[3] += ctl2[3];
   tmp[CRT_CNT_LAUNCHES] = ctx->launches + ctl[3];           // host launches + the kernels the graph loop ran
   tmp[CRT_CNT_WF_ITERATIONS] = ctx->wf_iterations + ctl[2];
   for (size_t i = 0; i < n; i++) out[i] = tmp[i];
@@ -1427,6 +1518,7 @@ int crt_reset_counters(crt_ctx* ctx) {
   CU(cudaSetDevice(ctx->device));
   CU(cudaMemsetAsync(ctx->d_counters, 0, CRT_NUM_COUNTERS * 8, ctx->stream));
   if (ctx->wf_mem) CU(cudaMemsetAsync(&ctx->wf.ctl->iters_total, 0, 8, ctx->stream));   // iters_total, launches_total
+  if (ctx->wf2_mem) CU(cudaMemsetAsync(&ctx->wf2.ctl->iters_total, 0, 8, ctx->stream));
   ctx->launches = 0;
   ctx->wf_iterations = 0;
   CU(drain_marks(ctx));

@@ -38,7 +38,7 @@ KERNEL_CLASSES = ["wf_logic", "wf_traverse", "wf_accumulate", "pt_megakernel", "
 
 # crt_params.wf_tuning / bvh_tuning bits (include/crt.h)
 WF_LIVE_ONE_LIST, WF_LIVE_ROUTED, WF_LIVE_CLASS = 1, 2, 3
-WF_DEFER_OFF, WF_DEFER_ON, WF_HOST_LOOP = 4, 8, 16
+WF_DEFER_OFF, WF_DEFER_ON, WF_HOST_LOOP, WF_ONE_LANE, WF_TWO_LANES_ALWAYS = 4, 8, 16, 32, 64
 WF_TAIL_SHIFT, WF_TAIL_OFF = 8, 31 << 8   # bits 8-12: v = 1..30 -> wf_tail takes over at <= 2^(v-1) live slots; 31: never
 BVH_EXACT_SLOTS, BVH_BUILDER_HOST_SAH, BVH_BUILDER_DEVICE = 0x200, 0x400, 0x800
 COMM_ID_BYTES = 128

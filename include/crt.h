@@ -102,6 +102,10 @@ typedef struct crt_params {
  * the GPU); with this bit the host launches every iteration and reads the live count back at check points (the round-1 form;
  * CRT_FLAG_KERNEL_TIMES and CRT_FLAG_WF_SPLIT imply it). */
 #define CRT_WF_HOST_LOOP 16u
+/* ... whether the device loop splits a chunk's samples over two half pools on two streams (default; hides the straggler phase
+ * at the end of every wf_traverse launch and the thin end of a chunk behind the other half's kernels) or keeps one (this bit) */
+#define CRT_WF_ONE_LANE 32u
+#define CRT_WF_TWO_LANES_ALWAYS 64u   /* two lanes also for chunks below 4 Mi work items (tests) */
 /* ... and when the iteration loop hands the chunk's last live slots to wf_tail (one thread runs a path to its end): bits
  * 8-12 = 0: the default (at most CRT_WF_TAIL_DEFAULT live slots and no work item left), v = 1 .. 30: at most 2^(v-1) slots,
  * 31: never (iterate until no slot is live, the round-1 form). */

@@ -289,6 +289,14 @@ def test_error_behaviour(gpu):
     r.set_scene(ps)
     r.frame(0)
     assert r.sample == 0
+    for bad in (dict(wf_tuning=4 | 8), dict(bvh_tuning=0x400 | 0x800), dict(kernel=7), dict(grid_size=0)):   # contradictory / unknown settings
+        with pytest.raises(CrtError) as e:
+            r.set_params(default_params(**bad))
+        assert e.value.code == 1   # CRT_ERR_ARG
+    with pytest.raises(CrtError) as e:
+        r.combine(1)               # one rank: nothing to exchange, but a destination that does not exist is still an error
+    assert e.value.code == 1
+    r.combine(0)                   # ... and rank 0 of 1 is a no-op that leaves the image as it is
     with pytest.raises(CrtError):
         r.accumulator(np.empty((16, 15, 4), dtype=np.float32))
     r.close()
@@ -380,14 +388,15 @@ def test_wavefront_pool_and_chunk_size_never_change_results(gpu, oracle, wf_slot
 
 
 @pytest.mark.parametrize("tail", [0, 31 << 8, 5 << 8, 13 << 8], ids=["tail_default", "tail_off", "tail_16", "tail_4096"])
-@pytest.mark.parametrize("host_loop", [0, 16], ids=["graph_loop", "host_loop"])
+@pytest.mark.parametrize("host_loop", [0, 16, 64, 32], ids=["graph_loop", "host_loop", "graph_two_lanes", "graph_one_lane"])
 @pytest.mark.parametrize("live,defer", [(1, 4), (2, 4), (3, 4), (3, 8), (2, 8)])
 @pytest.mark.parametrize("maker,kw", [(scenes.mesh_scene, dict(n_lon=64, n_lat=32)), (scenes.default_scene, {})])
 def test_wavefront_scheduling_forms_never_change_results(gpu, oracle, maker, kw, live, defer, host_loop, tail):
     """How wf_logic's live slots reach the next iteration (crt_params.wf_tuning: 1 one live list; 2 finish and bounce lists
     filled by wf_logic and wf_traverse; 3 class bytes + wf_partition -- in 2 and 3 a warp's lanes are in one phase, and with
     CRT_WF_DEFER_ON a path that ends in a bounce warp is finished by the next iteration's finish warps) and who runs the
-    iteration loop (the CUDA-graph WHILE node on the device, or the host) and when it hands the last live slots to wf_tail
+    iteration loop (the CUDA-graph WHILE node on the device -- over one pool, or over two half pools on two streams that
+    split the chunk's samples -- or the host) and when it hands the last live slots to wf_tail
     (never, at 16 / 4096 / the default 131072 slots) decide which thread runs which pixel-sample when, nothing else:
     accumulator, framebuffer and counters stay the oracle's.  A small pool forces many rounds per slot."""
     ps = maker(96, 64, **kw)
@@ -457,6 +466,23 @@ def test_builders_give_valid_trees_and_identical_hits(gpu, oracle, maker, kw, bu
     acc_c, fb_c, cc = oracle.scene(ps, default_params(max_depth=8)).render(2)
     assert_radiance(acc, acc_c, 2)
     assert np.array_equal(fb, fb_c) and cg == (int(cc[0]), int(cc[1]), int(cc[2]))
+    gpu.set_params(default_params())
+
+
+def test_host_tree_cache_is_not_fooled_by_a_reused_address(gpu, oracle):
+    """The host-built tree is cached per binding-8 buffer (a group builds it once for all members).  A cache keyed by the
+    buffer's ADDRESS matched a new scene allocated where a freed one had been and traversed a stale tree (found in round 2 as an
+    illegal access in the repack kernel); it is keyed by the owning pointer now.  Scenes of different triangle counts set one
+    after the other, many times, so that the allocator reuses addresses: hits always equal the oracle's linear scan."""
+    scs = [scenes.mesh_scene(32, 32, n_lon=64, n_lat=32), scenes.soup_scene(32, 32, n=4098), scenes.mesh_scene(32, 32, n_lon=32, n_lat=64)]
+    rays = scenes.camera_rays(scs[0], 3000, seed=6)
+    want = [oracle.scene(ps).trace_rays(rays) for ps in scs]
+    gpu.set_shard(0, 1, 0); gpu.set_params(default_params(bvh_tuning=0x400))
+    for rep in range(12):
+        k = rep % 3
+        gpu.set_scene(scs[k])
+        gi, gt = gpu.trace_rays(rays)
+        assert np.array_equal(gi, want[k][0]) and np.array_equal(gt.view(np.uint32), want[k][1].view(np.uint32)), rep
     gpu.set_params(default_params())
 
 
@@ -580,7 +606,8 @@ def _tri_light_scene(w, h):
     return scenes.with_triangle_lights(ps, lights)
 
 
-@pytest.mark.parametrize("tuning", [0, 16, (31 << 8), 16 | (31 << 8) | 2, 5 << 8], ids=["default", "host_loop", "no_tail", "host_routed_no_tail", "tail_16"])
+@pytest.mark.parametrize("tuning", [0, 16, (31 << 8), 16 | (31 << 8) | 2, 5 << 8, 64 | (5 << 8)],
+                         ids=["default", "host_loop", "no_tail", "host_routed_no_tail", "tail_16", "two_lanes_tail_16"])
 @pytest.mark.parametrize("kernel", KERNELS)
 def test_triangle_lights_radiance_parity(gpu, oracle, kernel, tuning):
     """A light that is itself a triangle: its shadow rays need CLOSEST-hit traversal (the linear list cannot find the light)

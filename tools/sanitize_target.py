@@ -25,6 +25,7 @@ def main():
         r.set_scene(ps)
         forms = [("wavefront, device loop, device tree", dict(kernel=KERNEL_WAVEFRONT, bvh_tuning=BVH_BUILDER_DEVICE, wf_slots=2048)),
                  ("wavefront, device loop, host tree, tail at 16", dict(kernel=KERNEL_WAVEFRONT, bvh_tuning=BVH_BUILDER_HOST_SAH, wf_slots=2048, wf_tuning=5 << 8)),
+                 ("wavefront, device loop, two lanes", dict(kernel=KERNEL_WAVEFRONT, wf_slots=2048, wf_tuning=64 | (5 << 8))),
                  ("wavefront, host loop, no tail", dict(kernel=KERNEL_WAVEFRONT, wf_slots=4096, wf_tuning=WF_HOST_LOOP | WF_TAIL_OFF)),
                  ("wavefront, routed lists", dict(kernel=KERNEL_WAVEFRONT, wf_slots=4096, wf_tuning=2 | WF_TAIL_OFF)),
                  ("wavefront, split kernels", dict(kernel=KERNEL_WAVEFRONT, wf_slots=4096, flags=4)),
