@@ -1147,14 +1147,14 @@ int crt_dispatch_frames(crt_ctx* ctx, uint32_t n) {
   uint32_t n_tiles = s.tiles_x * s.tiles_y;
   if (ctx->shard_mode == CRT_SHARD_TILES && ctx->world > 1) n_tiles = owned_tiles(ctx, ctx->rank, ctx->world);
   const uint32_t n_units = n_tiles * 32u;
-  // AUTO: the wavefront form when there is a BVH (ncu: the megakernel runs 4.75 of 32 lanes there) and, for linear-list
-  // scenes, whenever the dispatch has two frames or more.  Measured on the reference's default scene at 1080p
-  // (profiles/r01r_auto_threshold.txt), ms per dispatch of 1 / 2 / 4 / 64 frames: megakernel 2.2 / 4.4 / 8.3 / 125,
-  // wavefront 2.8 / 3.8 / 5.6 / 64 -- the wavefront pays ~2 ms per dispatch for the thin iterations of the paths that loop
-  // to max_depth inside the glass sphere and half the megakernel's time per frame after that.  Both forms give the same bits.
+  // AUTO: the wavefront form, whatever the scene and however many frames.  Round 1 kept the megakernel for single-frame
+  // dispatches of linear-list scenes (the reference's frame() on its own scene: 2.2 ms against 2.8 ms, because the wavefront
+  // paid ~2 ms of thin iterations for the paths that loop to max_depth inside the glass sphere); wf_tail removed those, and the
+  // same dispatch now takes 1.57 ms in the wavefront form against 2.25 ms in the megakernel, 2.75 against 4.49 ms for two frames
+  // (profiles/r02p_single_frame_cornell.txt).  The megakernel remains for max_depth > 1000 (the wavefront's per-iteration
+  // counters) and by name (CRT_KERNEL_MEGA).  Both forms give the same bits.
   uint32_t kernel = ctx->params.kernel;
-  if (kernel == CRT_KERNEL_AUTO)
-    kernel = (ctx->params.max_depth <= 1000 && (s.n_tri > 0 || n >= 2)) ? CRT_KERNEL_WAVEFRONT : CRT_KERNEL_MEGA;
+  if (kernel == CRT_KERNEL_AUTO) kernel = ctx->params.max_depth <= 1000 ? CRT_KERNEL_WAVEFRONT : CRT_KERNEL_MEGA;
   // (a light that is itself a triangle needs closest-hit shadow rays: both forms carry that path -- crt_device.cuh
   // shadow_intersect, crt_wavefront.cu NeeQuery::tri)
   CU(cudaEventRecord(ctx->ev_start, ctx->stream));
