@@ -1,0 +1,109 @@
+"""The C oracle against a second, independent reading of the shader (tests/wgsl_literal.py): bit for bit.
+
+The reference has no golden vectors and its WGSL cannot run on this box, so the oracle is "unpinned by the reference"
+(DESIGN.md section 2).  What CAN be checked is that two restatements of the shader written separately -- scalar Python that
+keeps the WGSL's structure, and the C the kernels are tested against -- agree on every bit of every pixel-sample, on the
+framebuffer bytes and on every statistic (rays, rand() calls, primitive tests, how each path ended): a misreading of the shader
+would have to be made twice.  The shared part is stated in wgsl_literal's header: where DESIGN section 3 puts an fmaf, and the
+sin / cos / exp / pow of include/crt_detmath.h.  The last test drops the fmaf choice and shows it is only rounding noise."""
+import numpy as np
+import pytest
+
+from computeraytracer_b200 import scenes
+from tests import orc
+from tests import wgsl_literal as wl
+
+
+@pytest.fixture(scope="module")
+def machine_parts(oracle):
+    def sincos(x):
+        s, c, _, _ = oracle.detmath(np.array([x], dtype=np.float32))
+        return s[0], c[0]
+
+    def exp(x):
+        return oracle.detmath(np.array([x], dtype=np.float32))[2][0]
+
+    def pow_1_2p4(x):
+        return oracle.detmath(np.array([x], dtype=np.float32))[3][0]
+    return sincos, exp, pow_1_2p4
+
+
+def _statistics(sh):
+    """In the order of include/crt.h's CRT_CNT_* 0..11 (4 and 5 are the BVH's: zero in a scene without triangles)."""
+    return [sh.paths, sh.rays_ext, sh.rays_shadow, sh.prim_tests, 0, 0, sh.n_rand, sh.term["miss"], sh.term["rr"], sh.term["light"],
+            sh.term["depth"], sh.depth_sum]
+
+
+def test_oracle_equals_the_literal_reading_bit_for_bit(oracle, machine_parts):
+    W = H = 32
+    ps = scenes.default_scene(W, H)
+    sh = wl.Shader(ps.bindings(), wl.Machine(*machine_parts, fused=True))
+    sc = oracle.scene(ps)
+    acc_l = np.zeros((H, W, 4), dtype=np.float32)                     # alt_color_buffer (CS:2): vec3 in 16-byte slots
+    for sample in (1, 2, 3):                                          # three dispatches, UpdateVariables.wgsl's sample++ before each
+        for y in range(H):
+            for x in range(W):
+                acc_l[y, x, :3] += np.array(sh.main(x, y, sample), dtype=np.float32)
+    assert sh.main(W, 0, 1) is None and sh.main(0, H, 1) is None      # CS:88: invocations outside the screen return
+    acc, fb, cnt = sc.render(3, threads=1)
+    assert np.array_equal(acc_l[..., :3].view(np.uint32), acc[..., :3].view(np.uint32))
+    assert _statistics(sh) == [int(c) for c in cnt[:12]]
+    fb_l = np.array([[sh.resolve(acc_l[y, x, :3], 3) for x in range(W)] for y in range(H)], dtype=np.uint8)
+    assert np.array_equal(fb_l, fb)
+    # the comparison means something only if the paths went everywhere the shader has code
+    assert sh.events["reflect"] > 50 and sh.events["refract"] > 200 and sh.events["attenuate"] > 100
+    assert sh.events["mis_light_hit"] > 5 and sh.term["light"] > sh.events["mis_light_hit"]
+    assert sh.term["miss"] > 500 and sh.term["rr"] > 500
+    assert np.count_nonzero(fb_l[..., :3]) > W * H
+
+
+def test_oracle_equals_the_literal_reading_other_sample_cells_and_depth_limit(oracle, machine_parts):
+    """sample = 18: `sample % GRID_SIZE` (CS:497) is 2, not the sample; MAXDEPTH = 2: the depth exit (CS:167) is taken often."""
+    W, H = 24, 16
+    ps = scenes.default_scene(W, H)
+    sh = wl.Shader(ps.bindings(), wl.Machine(*machine_parts, fused=True), max_depth=2)
+    sc = oracle.scene(ps, orc.default_params(max_depth=2))
+    acc, _, cnt = sc.render(1, sample_start=17, threads=1, want_fb=False)
+    got = np.array([[sh.main(x, y, 18) for x in range(W)] for y in range(H)], dtype=np.float32)
+    assert np.array_equal(got.view(np.uint32), acc[..., :3].view(np.uint32))
+    assert _statistics(sh) == [int(c) for c in cnt[:12]]
+    assert sh.term["depth"] > 20
+
+
+def test_the_fmaf_choice_is_rounding_noise(oracle, machine_parts):
+    """WGSL lets an implementation fuse a*b+c or not.  With every fmaf of section 3 replaced by two roundings the literal
+    reading stays within 1e-4 relative of the oracle on all but a handful of pixel-samples -- those whose path took a different
+    branch somewhere (a silhouette, a Russian-roulette draw): noise of the kind any two WGSL back ends show, not semantics."""
+    W = H = 32
+    ps = scenes.default_scene(W, H)
+    sh = wl.Shader(ps.bindings(), wl.Machine(*machine_parts, fused=False))
+    acc, _, _ = oracle.scene(ps).render(1, threads=1, want_fb=False)
+    got = np.array([[sh.main(x, y, 1) for x in range(W)] for y in range(H)], dtype=np.float32)
+    same = np.array_equal(got.view(np.uint32), acc[..., :3].view(np.uint32))
+    close = np.isclose(got, acc[..., :3], rtol=1e-4, atol=1e-6).all(axis=-1)
+    assert not same                                                    # the switch does something
+    assert (~close).sum() <= 8, int((~close).sum())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kernel", ["wavefront", "mega"])
+def test_cuda_path_equals_the_literal_reading_bit_for_bit(oracle, machine_parts, kernel):
+    """The same comparison without the C oracle in the middle: libcrt through the C ABI against the Python reading."""
+    from computeraytracer_b200.renderer import KERNEL_MEGA, KERNEL_WAVEFRONT, Renderer
+    W = H = 20
+    ps = scenes.default_scene(W, H)
+    sh = wl.Shader(ps.bindings(), wl.Machine(*machine_parts, fused=True))
+    acc_l = np.zeros((H, W, 3), dtype=np.float32)
+    for sample in (1, 2):
+        for y in range(H):
+            for x in range(W):
+                acc_l[y, x] += np.array(sh.main(x, y, sample), dtype=np.float32)
+    fb_l = np.array([[sh.resolve(acc_l[y, x], 2) for x in range(W)] for y in range(H)], dtype=np.uint8)
+    with Renderer(0) as r:
+        r.set_scene(ps)
+        r.set_params(kernel=KERNEL_MEGA if kernel == "mega" else KERNEL_WAVEFRONT)
+        r.frame(2)
+        acc, fb, c = r.accumulator(), r.framebuffer(), r.counters()
+    assert np.array_equal(acc[..., :3].view(np.uint32), acc_l.view(np.uint32))
+    assert np.array_equal(fb, fb_l)
+    assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == (sh.paths, sh.rays_ext, sh.rays_shadow)
