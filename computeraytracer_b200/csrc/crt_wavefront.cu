@@ -29,6 +29,9 @@
 #ifndef WF_LOGIC_BLOCK
 #define WF_LOGIC_BLOCK WF_BLOCK
 #endif
+#ifndef WF_PREFETCH
+#define WF_PREFETCH 11       // wf_logic<.., PF = true>, bit k: 32-byte sector k (A..E) of the record a thread handles in its NEXT trip is sent to L2
+#endif
 #ifndef WF_LOGIC_MIN_BLOCKS
 #define WF_LOGIC_MIN_BLOCKS 3   // 3 x 256 threads per SM = 85 registers at most (ptxas picks 106 without the bound)
 #endif
@@ -551,7 +554,7 @@ __global__ void __launch_bounds__(WF_BLOCK, WF_REGEN_MIN_BLOCKS) wf_regen(const 
 // hit (wf_bounce), and if the path ended finish it and start the slot's next path right here.  Lanes of a warp are in
 // different phases (ncu: ~17 of 32 active), but these kernels wait on memory and on dependent arithmetic rather than on
 // issue slots, and the fused form makes one pass over a slot's record per bounce instead of up to two.
-template <bool STATS, bool TRI>   // TRI: the scene has a triangle light (sc.shadow_closest); every other scene runs the variant without that code
+template <bool STATS, bool TRI, bool PF>   // TRI: the scene has a triangle light (sc.shadow_closest); PF: it has a BVH (record prefetch, below)
 __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(const __grid_constant__ DevScene sc, const WfState w, uint32_t it_arg,
                                                      uint32_t routed, unsigned long long* __restrict__ counters) {
   extern __shared__ float s_tables[];
@@ -593,6 +596,11 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
     Rng rng;
     NeeQuery nee; nee.pending = false; nee.tri = false; nee.light_prim = 0;
     const bool valid = i < n_cur && (i >= n_fin_pad || i < n_fin);   // not a padding lane of the finish list
+    // PF: the slot this thread handles in its NEXT trip -- its list entry is fetched now, its record is prefetched further down
+    const uint32_t i_next = i + stride;
+    const bool pf = PF && it != 0 && i_next < n_cur && (i_next >= n_fin_pad || i_next < n_fin);
+    uint32_t slot_next = 0;
+    if (PF) { if (pf) slot_next = i_next < n_fin_pad ? fin[i_next] : cur[i_next - n_fin_pad]; }
     if (valid) {
       need = true;
       if (it == 0) {
@@ -635,6 +643,18 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
         }
         if (!alive) wf_finish(sc, ck, cie, ps.L, ps.lam0, wid);
         else if (store_L) { rec_st(w, slot, WF_R_S2, ps.L); flags &= ~WF_FLAG_LZERO; }
+      }
+    }
+    if (PF) {
+      // Records live in a pool far larger than L2 and a pass finds them in DRAM; the list gives the address a whole trip ahead.
+      // Sectors A, B, D (what every pass reads).  r02t/r02u A/B, mesh1m: wf_logic 150.8 -> 142.7 ms; C and E on top change
+      // nothing, L1 instead of L2 neither.  Only in the instantiation for scenes with a BVH: in the reference's own scene the pass
+      // is bound by its arithmetic and the extra registers cost 2.5 % even when the prefetch is skipped at run time.
+      if (pf) {
+        const char* p = reinterpret_cast<const char*>(rec_ptr(w, slot_next, 0));
+#pragma unroll
+        for (int k = 0; k < 5; k++)
+          if ((WF_PREFETCH >> k) & 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 32 * k));
       }
     }
     // ---- slots whose path ended (or fresh slots) take the next (sample, pixel) work item: one atomic per warp.  (Dealing a
@@ -1071,11 +1091,13 @@ cudaError_t wf_config(bool stats, size_t smem, int* logic_blocks_per_sm, int* sh
                       int* trav_blocks_per_sm) {
   cudaError_t e;
 #define CRT_WF_CFG(S)                                                                                                              \
-  if ((e = cudaFuncSetAttribute(wf_logic<S, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
-  if ((e = cudaFuncSetAttribute(wf_logic<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaFuncSetAttribute(wf_logic<S, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaFuncSetAttribute(wf_logic<S, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaFuncSetAttribute(wf_logic<S, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
+  if ((e = cudaFuncSetAttribute(wf_logic<S, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
   if ((e = cudaFuncSetAttribute(wf_shade<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
   if ((e = cudaFuncSetAttribute(wf_regen<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;    \
-  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<S, true>, WF_LOGIC_BLOCK, smem)) != cudaSuccess) return e; \
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(logic_blocks_per_sm, wf_logic<S, true, true>, WF_LOGIC_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(shade_blocks_per_sm, wf_shade<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(regen_blocks_per_sm, wf_regen<S>, WF_BLOCK, smem)) != cudaSuccess) return e; \
   if ((e = cudaFuncSetAttribute(wf_tail<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;     \
@@ -1090,15 +1112,20 @@ cudaError_t launch_wf_begin(const WfState& w, const WfChunk& ck, cudaStream_t s)
   return cudaGetLastError();
 }
 
+// The instantiation of wf_logic a scene runs: with the triangle-light code only if a light is a triangle, with the record
+// prefetch only if the scene has a BVH.
+typedef void (*WfLogicFn)(const DevScene, const WfState, uint32_t, uint32_t, unsigned long long*);
+template <bool S>
+static WfLogicFn wf_logic_pick(const DevScene& sc) {
+  const bool pf = sc.n_nodes != 0u;
+  if (sc.shadow_closest) return pf ? wf_logic<S, true, true> : wf_logic<S, true, false>;
+  return pf ? wf_logic<S, false, true> : wf_logic<S, false, false>;
+}
+static WfLogicFn wf_logic_fn(const DevScene& sc, bool stats) { return stats ? wf_logic_pick<true>(sc) : wf_logic_pick<false>(sc); }
+
 cudaError_t launch_wf_logic(const DevScene& sc, const WfState& w, bool stats, uint32_t live_mode, int grid, size_t smem, uint32_t it,
                             unsigned long long* counters, cudaStream_t s) {
-  if (sc.shadow_closest) {
-    if (stats) wf_logic<true, true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
-    else wf_logic<false, true><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
-  } else {
-    if (stats) wf_logic<true, false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
-    else wf_logic<false, false><<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
-  }
+  wf_logic_fn(sc, stats)<<<grid, WF_LOGIC_BLOCK, smem, s>>>(sc, w, it, live_mode, counters);
   return cudaGetLastError();
 }
 
@@ -1169,8 +1196,7 @@ cudaError_t wf_graph_build(const DevScene& sc, const WfState& w, bool stats, uin
   };
   {
     void* args[] = {(void*)&sc, (void*)&w, &it, &logic_mode, &counters};
-    void* f = sc.shadow_closest ? (stats ? (void*)wf_logic<true, true> : (void*)wf_logic<false, true>)
-                                : (stats ? (void*)wf_logic<true, false> : (void*)wf_logic<false, false>);
+    void* f = (void*)wf_logic_fn(sc, stats);
     e = add(f, dim3(grid_l), dim3(WF_LOGIC_BLOCK), smem, args);
     if (e != cudaSuccess) { cudaGraphDestroy(g); return e; }
   }

@@ -6,10 +6,13 @@ keeps the WGSL's structure, and the C the kernels are tested against -- agree on
 framebuffer bytes and on every statistic (rays, rand() calls, primitive tests, how each path ended): a misreading of the shader
 would have to be made twice.  The shared part is stated in wgsl_literal's header: where DESIGN section 3 puts an fmaf, and the
 sin / cos / exp / pow of include/crt_detmath.h.  The last test drops the fmaf choice and shows it is only rounding noise."""
+import dataclasses
+
 import numpy as np
 import pytest
 
 from computeraytracer_b200 import scenes
+from computeraytracer_b200.scene_loader import PRIM_DTYPE, copy_records
 from tests import orc
 from tests import wgsl_literal as wl
 
@@ -68,6 +71,44 @@ def test_oracle_equals_the_literal_reading_other_sample_cells_and_depth_limit(or
     assert np.array_equal(got.view(np.uint32), acc[..., :3].view(np.uint32))
     assert _statistics(sh) == [int(c) for c in cnt[:12]]
     assert sh.term["depth"] > 20
+
+
+def _two_light_scene(W, H):
+    """The default scene plus a second light whose emission index (1) is in range for `lights[emission_index]` (CS:362 looks a
+    light up by its SPECTRUM index: out of range -- clamped -- for the default light, the wrong light's area for this one; both
+    readings must make the same 'mistake'), a tilted glass pane (glass on a patch, both faces), a small sphere, another camera."""
+    ps = scenes.default_scene(W, H)
+    n = ps.primitives.shape[0]
+    extra = np.zeros(3, dtype=PRIM_DTYPE)
+    extra[0] = (0, (1.0, 200.0, 150.0), (0.0, 120.0, 0.0), (0.0, 0.0, 160.0), (1, 0, 1, n))
+    extra[1] = (0, (120.0, 40.0, 30.0), (300.0, 40.0, 35.0), (-20.0, 260.0, 60.0), (4, 0, 2, n + 1))
+    extra[2] = (1, (430.0, 40.0, 120.0), (40.0, 40.0, 40.0), (0.0, 0.0, 0.0), (4, 1, 0, n + 2))
+
+    def raw(a):
+        return np.ascontiguousarray(a).view(np.uint8).tobytes()
+    cam = ps.camera.copy()
+    cam[0:3] = (300.0, 320.0, -700.0)
+    cam[4:7] = (260.0, 250.0, 0.0)
+    cam[8:11] = (0.1, 1.0, 0.05)
+    return dataclasses.replace(ps, primitives=copy_records(raw(ps.primitives) + raw(extra), PRIM_DTYPE),
+                               lights=copy_records(raw(ps.lights) + raw(extra[:1]), PRIM_DTYPE), camera=cam)
+
+
+def test_oracle_equals_the_literal_reading_two_lights_glass_pane(oracle, machine_parts):
+    W = H = 24
+    ps = _two_light_scene(W, H)
+    sh = wl.Shader(ps.bindings(), wl.Machine(*machine_parts, fused=True))
+    acc_l = np.zeros((H, W, 3), dtype=np.float32)
+    for sample in (1, 2):
+        for y in range(H):
+            for x in range(W):
+                acc_l[y, x] += np.array(sh.main(x, y, sample), dtype=np.float32)
+    acc, fb, cnt = oracle.scene(ps).render(2, threads=1)
+    assert np.array_equal(acc_l.view(np.uint32), acc[..., :3].view(np.uint32))
+    assert _statistics(sh) == [int(c) for c in cnt[:12]]
+    fb_l = np.array([[sh.resolve(acc_l[y, x], 2) for x in range(W)] for y in range(H)], dtype=np.uint8)
+    assert np.array_equal(fb_l, fb)
+    assert sh.events["refract"] > 300 and sh.events["mis_light_hit"] > 10 and sh.term["light"] > 30
 
 
 def test_the_fmaf_choice_is_rounding_noise(oracle, machine_parts):
