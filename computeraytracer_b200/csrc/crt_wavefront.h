@@ -7,15 +7,24 @@ struct DevScene;
 
 #define CRT_WF_MAX_ITERS 8192   // per-iteration counters are indexed by iteration and never reset inside a dispatch
 
-// Queue lengths of one iteration (32 bytes).  Indexed by iteration, so nothing is reset inside a dispatch.
+// Queue lengths of one iteration.  Indexed by iteration, so nothing is reset inside a dispatch.  Every counter that takes
+// atomics from all warps of a kernel sits in a 128-byte line of its own: with all of them in one 32-byte sector the atomics of
+// the BVH queue, the shadow queue and the fetch cursor went through one L2 atomic unit (r02x A/B: wf_logic 143.1 -> 141.7 ms with
+// 128-byte blocks, 140.1 with 1 KB blocks -- whose 33 MB memset per chunk is not worth it).
+#ifndef WF_ITER_SPREAD
+#define WF_ITER_SPREAD 32   // 32-bit words per block
+#endif
 struct WfIter {
   uint32_t n_bounce;   // slots whose extension ray hit a surface: wf_shade
   uint32_t n_finish;   // slots whose path is over (miss, or only an NEE answer was outstanding): wf_regen finishes them
   uint32_t n_regen;    // slots freed by wf_shade in this iteration: wf_regen starts new paths on them
+  uint32_t pad_a[WF_ITER_SPREAD - 3];
   uint32_t n_bvh;      // extension rays queued for the BVH in this iteration
+  uint32_t pad_b[WF_ITER_SPREAD - 1];
   uint32_t n_fetch;    // wf_traverse's fetch cursor into the BVH queue
+  uint32_t pad_c[WF_ITER_SPREAD - 1];
   uint32_t n_shadow;   // NEE shadow rays queued for the BVH in this iteration (traversed after the extension rays)
-  uint32_t pad[2];
+  uint32_t pad_d[WF_ITER_SPREAD - 1];
 };
 
 #define CRT_WF_SLOW_RAYS 64
