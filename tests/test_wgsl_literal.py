@@ -127,12 +127,13 @@ def test_the_fmaf_choice_is_rounding_noise(oracle, machine_parts):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("scene", ["default", "two_lights"])
 @pytest.mark.parametrize("kernel", ["wavefront", "mega"])
-def test_cuda_path_equals_the_literal_reading_bit_for_bit(oracle, machine_parts, kernel):
+def test_cuda_path_equals_the_literal_reading_bit_for_bit(oracle, machine_parts, kernel, scene):
     """The same comparison without the C oracle in the middle: libcrt through the C ABI against the Python reading."""
     from computeraytracer_b200.renderer import KERNEL_MEGA, KERNEL_WAVEFRONT, Renderer
     W = H = 20
-    ps = scenes.default_scene(W, H)
+    ps = scenes.default_scene(W, H) if scene == "default" else _two_light_scene(W, H)
     sh = wl.Shader(ps.bindings(), wl.Machine(*machine_parts, fused=True))
     acc_l = np.zeros((H, W, 3), dtype=np.float32)
     for sample in (1, 2):
@@ -148,3 +149,21 @@ def test_cuda_path_equals_the_literal_reading_bit_for_bit(oracle, machine_parts,
     assert np.array_equal(acc[..., :3].view(np.uint32), acc_l.view(np.uint32))
     assert np.array_equal(fb, fb_l)
     assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == (sh.paths, sh.rays_ext, sh.rays_shadow)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kernel", ["wavefront", "mega"])
+def test_cuda_path_two_lights_glass_pane_larger(oracle, kernel):
+    """The variant scene at a size the Python reading would take minutes for: libcrt against the C oracle, 96x96 x 5 frames."""
+    from computeraytracer_b200.renderer import KERNEL_MEGA, KERNEL_WAVEFRONT, Renderer
+    ps = _two_light_scene(96, 96)
+    acc_c, fb_c, cc = oracle.scene(ps).render(5)
+    with Renderer(0) as r:
+        r.set_scene(ps)
+        r.set_params(kernel=KERNEL_MEGA if kernel == "mega" else KERNEL_WAVEFRONT)
+        r.frame(2)
+        r.frame(3)
+        acc, fb, c = r.accumulator(), r.framebuffer(), r.counters()
+    assert np.array_equal(acc[..., :3].view(np.uint32), acc_c[..., :3].view(np.uint32))
+    assert np.array_equal(fb, fb_c)
+    assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == (int(cc[0]), int(cc[1]), int(cc[2]))
