@@ -111,6 +111,54 @@ def test_oracle_equals_the_literal_reading_two_lights_glass_pane(oracle, machine
     assert sh.events["refract"] > 300 and sh.events["mis_light_hit"] > 10 and sh.term["light"] > 30
 
 
+def _random_scene(seed, W, H):
+    """6-12 random patches and spheres with random materials and spectrum indices, 1-4 lights of either kind (a sphere as a light
+    has a zero `data3`: area 0, pdf inf, NaN radiance -- as undefined in the shader as here, but the same bits everywhere), a
+    random camera.  Nothing a scene file of the reference could not say."""
+    rng = np.random.default_rng(seed)
+    ps = scenes.default_scene(W, H)
+    n = int(rng.integers(6, 13))
+    prims = np.zeros(n, dtype=PRIM_DTYPE)
+    for i in range(n):
+        mat = 1 if i == 0 else int(rng.choice([0, 0, 0, 1, 2]))
+        idx = (int(rng.integers(0, 7)), int(rng.integers(0, 7)), mat, i)
+        if rng.random() < 0.6:
+            prims[i] = (0, tuple(rng.uniform(0, 555, 3)), tuple(rng.uniform(-300, 300, 3)), tuple(rng.uniform(-300, 300, 3)), idx)
+        else:
+            r = float(rng.uniform(20, 120))
+            prims[i] = (1, tuple(rng.uniform(50, 500, 3)), (r, r, r), (0, 0, 0), idx)
+
+    def raw(a):
+        return np.ascontiguousarray(a).view(np.uint8).tobytes()
+    lights = prims[[i for i in range(n) if prims[i]["data4"][2] == 1]]
+    cam = ps.camera.copy()
+    cam[0:3] = rng.uniform(-600, 1100, 3)
+    cam[4:7] = rng.uniform(150, 400, 3)
+    cam[8:11] = (0, 1, 0)
+    return dataclasses.replace(ps, primitives=copy_records(raw(prims), PRIM_DTYPE), lights=copy_records(raw(lights), PRIM_DTYPE), camera=cam)
+
+
+def _same_bits_or_both_nan(a, b):
+    return bool(((a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))).all())
+
+
+@pytest.mark.parametrize("seed", [2, 3, 4, 7])
+def test_oracle_equals_the_literal_reading_random_scenes(oracle, machine_parts, seed):
+    W = H = 16
+    ps = _random_scene(seed, W, H)
+    sh = wl.Shader(ps.bindings(), wl.Machine(*machine_parts, fused=True))
+    acc_l = np.zeros((H, W, 3), dtype=np.float32)
+    for sample in (1, 2):
+        for y in range(H):
+            for x in range(W):
+                acc_l[y, x] += np.array(sh.main(x, y, sample), dtype=np.float32)
+    acc, fb, cnt = oracle.scene(ps).render(2, threads=1)
+    assert _same_bits_or_both_nan(acc_l, acc[..., :3])
+    assert _statistics(sh) == [int(c) for c in cnt[:12]]
+    fb_l = np.array([[sh.resolve(acc_l[y, x], 2) for x in range(W)] for y in range(H)], dtype=np.uint8)
+    assert np.array_equal(fb_l, fb)
+
+
 def test_the_fmaf_choice_is_rounding_noise(oracle, machine_parts):
     """WGSL lets an implementation fuse a*b+c or not.  With every fmaf of section 3 replaced by two roundings the literal
     reading stays within 1e-4 relative of the oracle on all but a handful of pixel-samples -- those whose path took a different
@@ -167,3 +215,26 @@ def test_cuda_path_two_lights_glass_pane_larger(oracle, kernel):
     assert np.array_equal(acc[..., :3].view(np.uint32), acc_c[..., :3].view(np.uint32))
     assert np.array_equal(fb, fb_c)
     assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == (int(cc[0]), int(cc[1]), int(cc[2]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kernel", ["wavefront", "mega"])
+def test_cuda_path_random_scenes(oracle, kernel):
+    """libcrt against the C oracle on the random scenes (several lights, sphere lights, NaN radiance): accumulators bit for bit
+    (NaN = NaN: the GPU's canonical NaN has another payload than the host's), framebuffer bytes, ray counts."""
+    from computeraytracer_b200.renderer import KERNEL_MEGA, KERNEL_WAVEFRONT, Renderer
+    W = H = 48
+    with Renderer(0) as r:
+        r.set_params(kernel=KERNEL_MEGA if kernel == "mega" else KERNEL_WAVEFRONT)
+        for seed in range(12):
+            ps = _random_scene(seed, W, H)
+            acc_c, fb_c, cc = oracle.scene(ps).render(3)
+            r.set_scene(ps)
+            r.reset()
+            r.reset_counters()
+            r.frame(1)
+            r.frame(2)
+            acc, fb, c = r.accumulator(), r.framebuffer(), r.counters()
+            assert _same_bits_or_both_nan(acc[..., :3], acc_c[..., :3]), seed
+            assert np.array_equal(fb, fb_c), seed
+            assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == (int(cc[0]), int(cc[1]), int(cc[2])), seed
