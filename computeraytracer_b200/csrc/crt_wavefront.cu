@@ -127,6 +127,50 @@ __device__ __forceinline__ void wf_push(bool pred, uint32_t entry, uint32_t* __r
 // computed once the hit on the light is known (CS:393 needs its normal and position).  Then c carries beta as it was at the
 // bounce and aux = (cos_theta, reflectance index | light << 12, -, index of the linear list's hit); wf_tri_contribution
 // rebuilds BRDF, Le, the MIS weight and the product in the reference's order when the answer is there.
+// What an occluded query adds is (BRDF * 0) * beta (CS:407 then CS:187), not c * 0: the two differ when Le is not finite (a light
+// of zero area -- a sphere listed as a light -- has an infinite pdf) while BRDF and beta are.  A channel of c that is not finite
+// and would be 0 when occluded is stored as a NaN with a payload that arithmetic never produces (it returns 0x7FFFFFFF); the
+// payload says what the visible value was.  nee_resolve undoes it on either outcome.
+#define WF_NEE_NAN_ZERO 0x7FC0D0D0u   // visible: NaN, occluded: 0
+#define WF_NEE_PINF_ZERO 0x7FC0D0D1u  // visible: +inf, occluded: 0
+#define WF_NEE_NINF_ZERO 0x7FC0D0D2u  // visible: -inf, occluded: 0
+__device__ __forceinline__ bool nee_nonfinite(float x) { return (__float_as_uint(x) & 0x7F800000u) == 0x7F800000u; }
+__device__ __forceinline__ float nee_encode1(float c, float brdf, float beta) {
+  if (!nee_nonfinite(c)) return c;
+  const float c0 = (brdf * 0.0f) * beta;
+  if (c0 != c0) return c;   // NaN when occluded too: c * 0 says the same
+  return __uint_as_float(c != c ? WF_NEE_NAN_ZERO : (c > 0.0f ? WF_NEE_PINF_ZERO : WF_NEE_NINF_ZERO));
+}
+// (the rare paths are calls: inlined they cost wf_logic registers it does not have)
+__device__ __noinline__ float4 nee_encode_slow(float4 c, float4 brdf, float4 beta) {
+  return make_float4(nee_encode1(c.x, brdf.x, beta.x), nee_encode1(c.y, brdf.y, beta.y), nee_encode1(c.z, brdf.z, beta.z), nee_encode1(c.w, brdf.w, beta.w));
+}
+#ifndef WF_NEE_EXACT
+#define WF_NEE_EXACT 1   // A/B switch: 0 = c * 0 for an occluded query, as before (wrong bits when Le is not finite)
+#endif
+__device__ __forceinline__ float4 nee_encode(float4 c, float4 brdf, float4 beta) {
+  if (!WF_NEE_EXACT) return c;
+  if (!nee_nonfinite((c.x + c.y) + (c.z + c.w))) return c;   // all channels finite (a sum that overflows takes the call, which leaves finite channels alone)
+  return nee_encode_slow(c, brdf, beta);
+}
+__device__ __forceinline__ float nee_resolve1(float c, bool occluded) {
+  const uint32_t b = __float_as_uint(c);
+  if (b - WF_NEE_NAN_ZERO <= 2u) {
+    if (occluded) return 0.0f;
+    return b == WF_NEE_NAN_ZERO ? __uint_as_float(0x7FFFFFFFu) : __uint_as_float(b == WF_NEE_PINF_ZERO ? 0x7F800000u : 0xFF800000u);
+  }
+  return occluded ? c * 0.0f : c;
+}
+__device__ __noinline__ float4 nee_resolve_slow(float4 c, bool occluded) {
+  return make_float4(nee_resolve1(c.x, occluded), nee_resolve1(c.y, occluded), nee_resolve1(c.z, occluded), nee_resolve1(c.w, occluded));
+}
+// the contribution of a (non-triangle-light) query once its answer is known
+__device__ __forceinline__ float4 nee_resolve(float4 c, bool occluded) {
+  if (WF_NEE_EXACT && nee_nonfinite((c.x + c.y) + (c.z + c.w))) return nee_resolve_slow(c, occluded);
+  if (occluded) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }
+  return c;
+}
+
 struct NeeQuery {
   bool pending;
   bool tri;
@@ -244,7 +288,7 @@ __device__ __forceinline__ int wf_bounce(const DevScene& sc, const float* __rest
     const float4 c = make_float4((BRDF.x * le.x) * ps.beta.x, (BRDF.y * le.y) * ps.beta.y, (BRDF.z * le.z) * ps.beta.z,
                                  (BRDF.w * le.w) * ps.beta.w);                 // CS:187
     if (add_now) { ps.L.x += c.x; ps.L.y += c.y; ps.L.z += c.z; ps.L.w += c.w; }
-    else nee.c = nee.tri ? ps.beta : c;   // (a triangle light's contribution is computed when its hit is known: beta as it is now)
+    else nee.c = nee.tri ? ps.beta : nee_encode(c, BRDF, ps.beta);   // (a triangle light's contribution is computed when its hit is known: beta as it is now)
     const float u = rnd(rng), v = rnd(rng);
     if (STATS) st.rand_calls += 5;
     float pdf;
@@ -316,8 +360,7 @@ __device__ __forceinline__ float4 wf_pending(const DevScene& sc, const float* __
       return wf_tri_contribution(sc, spectra, v3(a), v3(q), q.w, m.z, __float_as_uint(aux.z), c, aux, (m.y >> 20) & 0x7FFu, !occluded);
     }
   }
-  if (occluded) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407: Le = 0, the sum still happens
-  return c;
+  return nee_resolve(c, occluded);   // CS:407: Le = 0, the sum still happens
 }
 template <bool TRI>
 __device__ __forceinline__ void wf_add_pending(const DevScene& sc, const float* __restrict__ spectra, const WfState& w, uint32_t slot, float4& L) {
@@ -738,7 +781,7 @@ __global__ void __launch_bounds__(WF_BLOCK) wf_tail(const __grid_constant__ DevS
           } else {
             Hit hs; hs.t = nee.t; hs.idx = nee.light_prim; hs.ref = 0;
             traverse<true, STATS>(sc, ps.o, nee.d, ps.exclude, sc.t_min, hs, st);
-            if (hs.idx != nee.light_prim) { c.x *= 0.0f; c.y *= 0.0f; c.z *= 0.0f; c.w *= 0.0f; }   // CS:407, as wf_pending does
+            c = nee_resolve(c, hs.idx != nee.light_prim);   // CS:407, as wf_pending does
           }
           ps.L.x += c.x; ps.L.y += c.y; ps.L.z += c.z; ps.L.w += c.w;
           lc.n_bvh_rays++;

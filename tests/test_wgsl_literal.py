@@ -238,3 +238,48 @@ def test_cuda_path_random_scenes(oracle, kernel):
             assert _same_bits_or_both_nan(acc[..., :3], acc_c[..., :3]), seed
             assert np.array_equal(fb, fb_c), seed
             assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == (int(cc[0]), int(cc[1]), int(cc[2])), seed
+
+
+def _random_scene_with_triangles(seed, W, H):
+    """A random scene (above) plus 40-400 random triangles (this project's category 2) of random materials -- diffuse, light,
+    glass -- every light-material primitive also listed in the lights binding."""
+    ps = _random_scene(seed, W, H)
+    rng = np.random.default_rng(1000 + seed)
+    n0 = ps.primitives.shape[0]
+    nt = int(rng.integers(40, 401))
+    tris = np.zeros(nt, dtype=PRIM_DTYPE)
+    for i in range(nt):
+        mat = int(rng.choice([0, 0, 0, 0, 1, 2, 2]))
+        size = float(rng.choice([15.0, 60.0, 250.0]))
+        tris[i] = (2, tuple(rng.uniform(0, 555, 3)), tuple(rng.uniform(-size, size, 3)), tuple(rng.uniform(-size, size, 3)),
+                   (int(rng.integers(0, 7)), int(rng.integers(0, 7)), mat, n0 + i))
+
+    def raw(a):
+        return np.ascontiguousarray(a).view(np.uint8).tobytes()
+    prims = copy_records(raw(ps.primitives) + raw(tris), PRIM_DTYPE)
+    lights = prims[[i for i in range(prims.shape[0]) if prims[i]["data4"][2] == 1]]
+    return dataclasses.replace(ps, primitives=prims, lights=copy_records(raw(lights), PRIM_DTYPE))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("builder", ["host", "device"])
+@pytest.mark.parametrize("kernel", ["wavefront", "mega"])
+def test_cuda_path_random_scenes_with_triangles(oracle, kernel, builder):
+    """The same with triangles in the scene (BVH traversal, triangle lights, glass triangles): libcrt against the oracle's linear scan."""
+    from computeraytracer_b200.renderer import BVH_BUILDER_DEVICE, BVH_BUILDER_HOST_SAH, KERNEL_MEGA, KERNEL_WAVEFRONT, Renderer
+    W = H = 40
+    with Renderer(0) as r:
+        r.set_params(kernel=KERNEL_MEGA if kernel == "mega" else KERNEL_WAVEFRONT, max_depth=12,
+                     bvh_tuning=BVH_BUILDER_DEVICE if builder == "device" else BVH_BUILDER_HOST_SAH)
+        for seed in range(8):
+            ps = _random_scene_with_triangles(seed, W, H)
+            acc_c, fb_c, cc = oracle.scene(ps, orc.default_params(max_depth=12)).render(3)
+            r.set_scene(ps)
+            r.reset()
+            r.reset_counters()
+            r.frame(1)
+            r.frame(2)
+            acc, fb, c = r.accumulator(), r.framebuffer(), r.counters()
+            assert _same_bits_or_both_nan(acc[..., :3], acc_c[..., :3]), seed
+            assert np.array_equal(fb, fb_c), seed
+            assert (c["paths"], c["rays_ext"], c["rays_shadow"]) == (int(cc[0]), int(cc[1]), int(cc[2])), seed
