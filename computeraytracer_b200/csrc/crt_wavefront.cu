@@ -216,7 +216,7 @@ __device__ __forceinline__ float4 wf_tri_contribution(const DevScene& sc, const 
 // before anything else is added to L, so the order of the float additions is the reference's.
 // Returns 0: the path ended; 1: it continues with an extension ray; 2: Russian roulette ended it while nee.pending
 // (the slot must live on until the contribution has been added).
-template <bool STATS, bool TRI>
+template <bool STATS, bool TRI, bool BVH = true>   // BVH = false: the scene has no triangles, so no NEE query is ever left pending
 __device__ __forceinline__ int wf_bounce(const DevScene& sc, const float* __restrict__ spectra, PathState& ps, Rng& rng, const Hit& h,
                                          Stats& st, uint32_t* term, uint32_t& n_shadow, NeeQuery& nee) {
   uint32_t lam[4];
@@ -271,7 +271,7 @@ __device__ __forceinline__ int wf_bounce(const DevScene& sc, const float* __rest
       const float pdf_b = crt_div(cos_theta, CRT_PI_F);
       const float w = power_heuristic(pdf_l, pdf_b);
       le = make_float4(crt_div(le.x * w, pdf_l), crt_div(le.y * w, pdf_l), crt_div(le.z * w, pdf_l), crt_div(le.w * w, pdf_l));  // CS:400
-      if (hits_root_box(sc, s.position, light_dir, hs.t)) {   // a triangle may still occlude: any-hit query bounded by the light
+      if (BVH && hits_root_box(sc, s.position, light_dir, hs.t)) {   // a triangle may still occlude: any-hit query bounded by the light
         add_now = false;
         nee.pending = true; nee.d = light_dir; nee.t = hs.t; nee.light_prim = include;
       }
@@ -656,7 +656,7 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
         // most one term, CS:152 / CS:156 / CS:187; 0 + c = c), and L is fetched afterwards only if that term is not all
         // zeros (L is never -0, so L + 0 = L bit for bit; a NaN term is not "all zeros") or the path ended.
         wf_load(w, slot, ps, rng, wid, flags);
-        const bool had_pending = (flags & WF_FLAG_PENDING) != 0u;
+        const bool had_pending = PF && (flags & WF_FLAG_PENDING) != 0u;   // (without triangles no query is ever left pending)
         const uint32_t lzero = flags & WF_FLAG_LZERO;
         if (had_pending) { ps.L = wf_load_L(w, slot, lzero); wf_add_pending<TRI>(sc, spectra, w, slot, ps.L); }
         int r = 0;
@@ -664,7 +664,7 @@ __global__ void __launch_bounds__(WF_LOGIC_BLOCK, WF_LOGIC_MIN_BLOCKS) wf_logic(
           const float4 hv = rec_ld(w, slot, WF_R_H);
           Hit h; h.t = hv.x; h.idx = __float_as_uint(hv.y); h.ref = __float_as_uint(hv.z);
           uint32_t term = 0;
-          r = wf_bounce<STATS, TRI>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
+          r = wf_bounce<STATS, TRI, PF>(sc, spectra, ps, rng, h, st, &term, lc.n_shadow, nee);
           if (STATS && r != 1) { lc.term_cnt[term - TERM_MISS]++; lc.depth_sum += ps.depth; }
           // routed forms with WF_LIVE_DEFER: a path that ends in a warp of the bounce list (light hit, depth limit, Russian
           // roulette) is not finished here by the few lanes it happens to -- the slot goes to the finish list as a dead
@@ -1160,7 +1160,7 @@ cudaError_t launch_wf_begin(const WfState& w, const WfChunk& ck, cudaStream_t s)
 typedef void (*WfLogicFn)(const DevScene, const WfState, uint32_t, uint32_t, unsigned long long*);
 template <bool S>
 static WfLogicFn wf_logic_pick(const DevScene& sc) {
-  const bool pf = sc.n_nodes != 0u;
+  const bool pf = sc.n_tri != 0u;   // (hits_root_box, the only source of pending NEE queries, says no without triangles)
   if (sc.shadow_closest) return pf ? wf_logic<S, true, true> : wf_logic<S, true, false>;
   return pf ? wf_logic<S, false, true> : wf_logic<S, false, false>;
 }
