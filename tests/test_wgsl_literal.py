@@ -73,6 +73,24 @@ def test_oracle_equals_the_literal_reading_other_sample_cells_and_depth_limit(or
     assert sh.term["depth"] > 20
 
 
+def test_oracle_equals_the_literal_reading_other_parameters(oracle, machine_parts):
+    """crt_params that stand for the shader's constants: GRID_SIZE 4 (CS:15), t_min 0.01 (CS:720), exposure 1.0 (CS:112)."""
+    W, H = 20, 20
+    ps = scenes.default_scene(W, H)
+    sh = wl.Shader(ps.bindings(), wl.Machine(*machine_parts, fused=True), grid_size=4)
+    sc = oracle.scene(ps, orc.default_params(grid_size=4, t_min=0.01, exposure=1.0))
+    acc_l = np.zeros((H, W, 3), dtype=np.float32)
+    for sample in (5, 6):
+        for y in range(H):
+            for x in range(W):
+                acc_l[y, x] += np.array(sh.main(x, y, sample, t_min=0.01), dtype=np.float32)
+    acc, fb, cnt = sc.render(2, sample_start=4, threads=1)
+    assert np.array_equal(acc_l.view(np.uint32), acc[..., :3].view(np.uint32))
+    assert _statistics(sh) == [int(c) for c in cnt[:12]]
+    fb_l = np.array([[sh.resolve(acc_l[y, x], 6, exposure=1.0) for x in range(W)] for y in range(H)], dtype=np.uint8)
+    assert np.array_equal(fb_l, fb)
+
+
 def _two_light_scene(W, H):
     """The default scene plus a second light whose emission index (1) is in range for `lights[emission_index]` (CS:362 looks a
     light up by its SPECTRUM index: out of range -- clamped -- for the default light, the wrong light's area for this one; both
