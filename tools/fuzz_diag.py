@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Diagnostic for tests/test_wgsl_literal.py's random scenes: libcrt (a kernel form) against the oracle, per seed the number of
-pixels that differ and a few of them.    python tools/fuzz_diag.py [n_seeds]"""
+pixels that differ and a few of them.    python tools/fuzz_diag.py [n_seeds [first_seed]]"""
 import os
 import sys
 
@@ -15,10 +15,11 @@ from tests.test_wgsl_literal import _random_scene_with_triangles  # noqa: E402
 
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+    first = int(sys.argv[2]) if len(sys.argv) > 2 else 0
     o = orc.load()
     W = H = 40
     forms = [("mega", KERNEL_MEGA, 0), ("wavefront", KERNEL_WAVEFRONT, 0), ("wf_host_loop_no_tail", KERNEL_WAVEFRONT, WF_HOST_LOOP | WF_TAIL_OFF)]
-    for seed in range(n):
+    for seed in range(first, first + n):
         ps = _random_scene_with_triangles(seed, W, H)
         acc_c, fb_c, cc = o.scene(ps, orc.default_params(max_depth=12)).render(3)
         for name, k, tune in forms:
